@@ -1,0 +1,250 @@
+/*
+ * xetgpu.h — C ABI of the B200-native Xet content-addressing library (libxetgpu.so).
+ *
+ * The library computes, on one NVIDIA B200 (sm_100a), what OME reaches through
+ * huggingface/xet-core when model shards are content-addressed: gear content-defined
+ * chunk boundaries, keyed-BLAKE3 chunk hashes, the merkle root and the Xet file hash.
+ * Results are bit-exact with xet-core ("Parity").
+ *
+ * It sits BESIDE the reference's libxet (pkg/xet/xet.h) and follows its conventions
+ * (reference file:line in brackets):
+ *   - every fallible call returns XetError* — NULL means success; the caller frees a
+ *     non-NULL error with xetgpu_free_error            [pkg/xet/xet.h:86-90,132; src/error.rs:55]
+ *   - error codes are the reference's XetErrorCode values      [pkg/xet/src/error.rs:12-23]
+ *   - results come back through out-pointers, are owned by the library until the
+ *     matching xetgpu_free_* call, and every free function accepts NULL
+ *                                                       [pkg/xet/xet.h:132-134; src/ffi.rs:118]
+ *   - inputs are borrowed for the duration of the call; strings are NUL-terminated UTF-8
+ *   - calls are synchronous (the reference blocks on its runtime) [pkg/xet/src/ffi.rs:190]
+ *   - a context may be used from any thread; calls on one context are serialised
+ *     internally; it must not be used during xetgpu_context_free  [pkg/xet/README.md:76,88]
+ *   - progress / cancellation use the reference's callback shapes   [pkg/xet/xet.h:22-40]
+ *   - a no-op versioned symbol lets the cgo preamble fail at link time on a mismatch
+ *                                                       [pkg/xet/xet.h:94; pkg/xet/xet.go:11-13]
+ * No type in this header depends on CUDA or PyTorch; device pointers travel as void*.
+ */
+#ifndef XETGPU_H
+#define XETGPU_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- shared with pkg/xet/xet.h (identical layout; guarded so both headers can be included) */
+#ifndef XET_H
+typedef struct {
+    int32_t code;
+    char* message;
+    char* details;
+} XetError; /* [pkg/xet/xet.h:86-90] */
+
+typedef enum {
+    XET_PROGRESS_PHASE_SCANNING = 0,
+    XET_PROGRESS_PHASE_DOWNLOADING = 1,
+    XET_PROGRESS_PHASE_FINALIZING = 2,
+} XetProgressPhase; /* [pkg/xet/xet.h:15-19] */
+
+typedef struct {
+    XetProgressPhase phase;
+    uint64_t total_bytes;
+    uint64_t completed_bytes;
+    uint32_t total_files;
+    uint32_t completed_files;
+    const char* current_file;
+    uint64_t current_file_completed_bytes;
+    uint64_t current_file_total_bytes;
+} XetProgressUpdate; /* [pkg/xet/xet.h:21-30] */
+
+typedef void (*XetProgressCallback)(const XetProgressUpdate* update, void* user_data); /* [xet.h:32] */
+typedef bool (*XetCancellationCallback)(void* user_data);                               /* [xet.h:34] */
+typedef struct {
+    XetCancellationCallback callback;
+    void* user_data;
+} XetCancellationToken; /* [pkg/xet/xet.h:36-39] */
+#endif
+
+/* Error codes: the reference's XetErrorCode [pkg/xet/src/error.rs:12-23]. */
+enum {
+    XETGPU_OK = 0,
+    XETGPU_ERR_INVALID_CONFIG = 1,    /* NULL / malformed argument [src/ffi.rs:140-146] */
+    XETGPU_ERR_NOT_FOUND = 4,         /* file does not exist */
+    XETGPU_ERR_CHECKSUM_MISMATCH = 6, /* verify: computed hash != expected [src/error.rs:19] */
+    XETGPU_ERR_CANCELLED = 7,
+    XETGPU_ERR_IO = 8,
+    XETGPU_ERR_UNKNOWN = 99,          /* CUDA runtime failures land here, message = cudaGetErrorString */
+};
+
+/* Chunking constants of xet-core's deduplication crate. */
+#define XETGPU_TARGET_CHUNK 65536u
+#define XETGPU_MIN_CHUNK 8192u
+#define XETGPU_MAX_CHUNK 131072u
+
+typedef struct XetGpuContext XetGpuContext; /* opaque; one per (process, GPU) */
+
+/* Replaces nothing in xet.h: mirrors XetConfig's role [pkg/xet/xet.h:42-48] for the GPU path. */
+typedef struct {
+    int32_t device;             /* CUDA device ordinal; -1 = current device */
+    void* stream;               /* cudaStream_t to launch on; NULL = a stream the context owns */
+    uint64_t staging_bytes;     /* size of EACH of the two pinned host staging buffers used for
+                                   host->device ingestion; 0 = 64 MiB */
+    uint64_t max_batch_bytes;   /* xetgpu_hash_files: bytes resident on the device per batch;
+                                   0 = 8 GiB */
+    uint32_t flags;             /* XETGPU_CTX_* */
+} XetGpuConfig;
+
+#define XETGPU_CTX_STAGE_TIMING 1u /* record CUDA events around every stage (xetgpu_last_timings) */
+
+/* Where the bytes passed to xetgpu_hash_buffers live. */
+enum {
+    XETGPU_MEM_AUTO = 0,   /* ask cudaPointerGetAttributes */
+    XETGPU_MEM_HOST = 1,   /* host memory (pageable or pinned) */
+    XETGPU_MEM_DEVICE = 2, /* device memory on the context's GPU, 16-byte aligned */
+};
+
+#define XETGPU_WANT_CHUNKS 1u /* also return per-chunk end offsets and hashes */
+
+/* One file's result.  Hash bytes are in RAW DIGEST ORDER; the Xet hex form
+ * (MerkleHash::hex, four LE u64 words as %016x) is produced by xetgpu_hash_to_hex. */
+typedef struct {
+    uint8_t file_hash[32];   /* merklehash::file_hash of the chunk list */
+    uint8_t merkle_root[32]; /* merklehash::aggregated_node_hash (== xorb_hash over all chunks) */
+    uint64_t size;           /* bytes */
+    uint64_t n_chunks;
+    uint64_t first_chunk;    /* index of this file's first chunk in XetGpuResult.chunk_* */
+} XetGpuFileResult;
+
+typedef struct {
+    size_t n_files;
+    XetGpuFileResult* files;
+    uint64_t n_chunks;       /* 0 unless XETGPU_WANT_CHUNKS */
+    uint64_t* chunk_ends;    /* per chunk: exclusive end offset, relative to its own file */
+    uint8_t* chunk_hashes;   /* 32 bytes per chunk, raw digest order */
+} XetGpuResult;
+
+/* Device time of each stage of the last hash call, in milliseconds (CUDA events on the
+ * context's stream; only filled when the context has XETGPU_CTX_STAGE_TIMING). */
+typedef struct {
+    float h2d_ms;
+    float gear_ms;      /* K1: gear window hash + candidate compaction */
+    float resolve_ms;   /* K2: min/max boundary resolution */
+    float blake3_ms;    /* K3: leaf compression + chunk tree */
+    float merkle_ms;    /* K4: merkle levels + file hash */
+    float d2h_ms;
+    float total_ms;
+    uint64_t bytes;
+    uint64_t n_chunks;
+    uint64_t n_candidates;
+    uint32_t kernel_launches;
+} XetGpuTimings;
+
+/* Link-time version guard, same idea as xet_version_1_0_0 [pkg/xet/xet.h:94]. */
+extern void xetgpu_version_0_1_0(void);
+
+/* Context lifecycle — shaped like xet_client_new / xet_client_free [pkg/xet/xet.h:97-98],
+ * but returns an error object instead of a bare NULL so CUDA failures are reportable. */
+XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContext** out_ctx);
+void xetgpu_context_free(XetGpuContext* ctx);
+
+/* Same callback plumbing as xet_client_set_progress_callback [pkg/xet/xet.h:99-104]. */
+XetError* xetgpu_context_set_progress_callback(XetGpuContext* ctx, XetProgressCallback callback,
+                                               void* user_data, uint32_t throttle_ms);
+
+/*
+ * Hash n_files byte strings packed back to back in `data`: file f is
+ * data[offsets[f] .. offsets[f+1]).  offsets has n_files+1 ascending entries, offsets[0]
+ * may be non-zero.  This is the entry point for bytes already in memory (the replica
+ * agent's checksum switch [internal/ome-agent/replica/replicator/helper.go:86-109], or a
+ * download buffer).  Stands where xet-core's clean path would run
+ * (deduplication::Chunker + merklehash::{compute_data_hash,file_hash}).
+ */
+XetError* xetgpu_hash_buffers(XetGpuContext* ctx, const void* data, const uint64_t* offsets,
+                              size_t n_files, int32_t memory, uint32_t flags,
+                              XetGpuResult** out_result);
+
+/*
+ * Hash files on disk: read through the pinned staging buffers and copied to the GPU
+ * while earlier bytes are being hashed.  The verify-after-download entry point for
+ * model-agent [pkg/modelagent/gopher.go:1130-1149 has no verification today; the OCI
+ * branch's MD5 pass at gopher.go:843-860 is the shape it mirrors].
+ */
+XetError* xetgpu_hash_files(XetGpuContext* ctx, const char* const* paths, size_t n_files,
+                            uint32_t flags, const XetCancellationToken* cancel_token,
+                            XetGpuResult** out_result);
+
+/*
+ * Verify: compute the Xet file hash and compare with the 64-digit hex the Hub advertises
+ * (X-Xet-Hash header / tree API xetHash) [pkg/xet/src/xet_integration.rs:41-44;
+ * pkg/xet/src/hf_adapter.rs:36-44].  NULL = match; code 6 (ChecksumMismatch) with both
+ * hashes in `details` otherwise.  Shape precedent: hub.VerifyChecksum
+ * [pkg/hfutil/hub/utils.go:139-158].
+ */
+XetError* xetgpu_verify_file(XetGpuContext* ctx, const char* path, const char* expected_hex);
+XetError* xetgpu_verify_buffer(XetGpuContext* ctx, const void* data, uint64_t len, int32_t memory,
+                               const char* expected_hex);
+
+/* MerkleHash::hex / MerkleHash::from_hex [used at pkg/xet/src/xet_downloader.rs:124-126]. */
+void xetgpu_hash_to_hex(const uint8_t hash[32], char out_hex[65]);
+XetError* xetgpu_hash_from_hex(const char* hex, uint8_t out_hash[32]);
+
+/* ---- stage-level entry points (parity tests, benchmarks, multi-GPU range partitioning) ---- */
+
+/*
+ * K1 only: indices i (relative to `data`) whose 64-byte gear window hash has its 16 top
+ * bits clear (gearhash::Hasher::next_match semantics evaluated at every offset).  `data`
+ * is a device or host buffer of `len` bytes.  Returns a malloc'd ascending array
+ * (xetgpu_free_u64).
+ */
+XetError* xetgpu_gear_candidates(XetGpuContext* ctx, const void* data, uint64_t len, int32_t memory,
+                                 uint64_t** out_indices, uint64_t* out_count);
+
+/*
+ * Byte-range form for a file split across GPUs (BASELINE.json config 4).  `data` holds
+ * bytes [range_begin - lead, range_end) of ONE file of `file_len` bytes, where
+ * lead = min(range_begin, XETGPU_RANGE_LEAD).  `entry_cut` is the last chunk boundary
+ * <= range_begin as resolved by the previous range's owner (0 for the first range).
+ * Produces every chunk whose END lies in (range_begin, range_end] — ends are file-relative —
+ * plus `exit_cut`, the value to hand to the next range's owner.  No file hash is computed;
+ * rank 0 combines the per-range chunk lists with xetgpu_merkle_from_chunks.
+ */
+#define XETGPU_RANGE_LEAD (XETGPU_MAX_CHUNK + 64u)
+XetError* xetgpu_hash_range(XetGpuContext* ctx, const void* data, int32_t memory, uint64_t file_len,
+                            uint64_t range_begin, uint64_t range_end, uint64_t entry_cut,
+                            uint64_t* out_exit_cut, XetGpuResult** out_result);
+
+/*
+ * Boundary resolution is a carry chain across ranges; to keep ranks from waiting on one
+ * another, a range owner may first ask for the cut it WOULD hand on if its own entry were
+ * `assumed_entry_cut`, forward that, and only re-run when the true entry differs.
+ */
+XetError* xetgpu_range_exit_cut(XetGpuContext* ctx, const void* data, int32_t memory, uint64_t file_len,
+                                uint64_t range_begin, uint64_t range_end, uint64_t entry_cut,
+                                uint64_t* out_exit_cut);
+
+/* K4 only: merkle root + file hash of a host list of (hash, size) pairs, on the GPU
+ * (merklehash::aggregated_node_hash / file_hash). */
+XetError* xetgpu_merkle_from_chunks(XetGpuContext* ctx, const uint8_t* chunk_hashes,
+                                    const uint64_t* chunk_sizes, uint64_t n_chunks,
+                                    uint8_t out_merkle_root[32], uint8_t out_file_hash[32]);
+
+/* K0: fill device memory with the SURVEY.md §8(d) counter-based splitmix64 stream:
+ * dst[i] = byte (byte_off + i) of stream `seed`.  Benchmarks and tests only. */
+XetError* xetgpu_fill_splitmix(XetGpuContext* ctx, void* device_dst, uint64_t seed, uint64_t byte_off,
+                               uint64_t len);
+
+/* Stage timings of the most recent hash call on this context. */
+XetError* xetgpu_last_timings(XetGpuContext* ctx, XetGpuTimings* out);
+
+/* Memory management — all NULL-safe [pkg/xet/xet.h:132-134]. */
+void xetgpu_free_error(XetError* err);
+void xetgpu_free_result(XetGpuResult* result);
+void xetgpu_free_u64(uint64_t* array);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* XETGPU_H */

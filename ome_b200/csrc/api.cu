@@ -1,0 +1,923 @@
+// C ABI of libxetgpu.so (include/xetgpu.h): context, workspace, host<->device ingestion and the
+// stage pipeline.  Conventions follow the reference's libxet FFI (pkg/xet/src/ffi.rs, error.rs):
+// NULL == success, heap-allocated XetError otherwise, out-pointers for results, NULL-safe frees.
+//
+// There is no CPU fallback anywhere in this file: if the device or a kernel launch fails the call
+// returns an error.
+#include <cuda_runtime.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <chrono>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/xetgpu.h"
+#include "xetgpu_internal.h"
+
+using namespace xetgpu;
+
+namespace xetgpu {
+void init_chunk_hash_kernels();  // chunk_hash.cu
+void init_gear_kernels();        // gear.cu
+}  // namespace xetgpu
+
+// ------------------------------------------------------------------------------------ errors
+static char* dup_cstr(const std::string& s) {
+    char* p = (char*)malloc(s.size() + 1);
+    if (p) memcpy(p, s.c_str(), s.size() + 1);
+    return p;
+}
+
+static XetError* make_error(int32_t code, const std::string& message, const std::string& details = "") {
+    XetError* e = (XetError*)malloc(sizeof(XetError));
+    if (!e) return nullptr;
+    e->code = code;
+    e->message = dup_cstr(message);
+    e->details = details.empty() ? nullptr : dup_cstr(details);
+    return e;
+}
+
+static XetError* cuda_error(cudaError_t err, const char* what) {
+    return make_error(XETGPU_ERR_UNKNOWN, std::string("CUDA error in ") + what + ": " + cudaGetErrorString(err),
+                      cudaGetErrorName(err));
+}
+
+#define CU(expr)                                         \
+    do {                                                 \
+        cudaError_t _e = (expr);                         \
+        if (_e != cudaSuccess) return cuda_error(_e, #expr); \
+    } while (0)
+
+extern "C" void xetgpu_free_error(XetError* err) {
+    if (!err) return;
+    free(err->message);
+    free(err->details);
+    free(err);
+}
+
+extern "C" void xetgpu_version_0_1_0(void) {}
+
+// ----------------------------------------------------------------------------------- context
+struct Arena {
+    uint8_t* base = nullptr;
+    uint64_t cap = 0;
+    uint64_t used = 0;
+    template <typename T>
+    T* take(uint64_t count) {
+        uint64_t bytes = (count * sizeof(T) + 255) & ~255ull;
+        T* p = reinterpret_cast<T*>(base + used);
+        used += bytes;
+        return p;
+    }
+};
+
+struct XetGpuContext {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint32_t flags = 0;
+    uint64_t staging_bytes = 64ull << 20;
+    uint64_t max_batch_bytes = 8ull << 30;
+    std::mutex mu;
+    // workspace (grow-only)
+    Arena ws;
+    uint8_t* d_input = nullptr;  // device copy of host inputs
+    uint64_t d_input_cap = 0;
+    uint8_t* h_stage[2] = {nullptr, nullptr};  // pinned ingestion buffers
+    cudaEvent_t stage_free[2] = {nullptr, nullptr};
+    uint8_t* h_meta = nullptr;  // pinned metadata / readback area
+    uint64_t h_meta_cap = 0;
+    uint64_t cand_cap_hint = 0;
+    // timing
+    cudaEvent_t ev[8] = {};
+    XetGpuTimings last = {};
+    // progress
+    XetProgressCallback progress = nullptr;
+    void* progress_user = nullptr;
+    uint32_t throttle_ms = 0;
+    std::chrono::steady_clock::time_point last_progress;
+};
+
+static XetError* ensure_meta(XetGpuContext* c, uint64_t bytes) {
+    if (bytes <= c->h_meta_cap) return nullptr;
+    if (c->h_meta) cudaFreeHost(c->h_meta);
+    c->h_meta = nullptr;
+    c->h_meta_cap = 0;
+    uint64_t cap = std::max<uint64_t>(bytes * 2, 1 << 20);
+    CU(cudaMallocHost((void**)&c->h_meta, cap));
+    c->h_meta_cap = cap;
+    return nullptr;
+}
+
+static XetError* ensure_input(XetGpuContext* c, uint64_t bytes) {
+    bytes += 256;  // slack: kernels read whole 16-byte units
+    if (bytes <= c->d_input_cap) return nullptr;
+    if (c->d_input) cudaFree(c->d_input);
+    c->d_input = nullptr;
+    c->d_input_cap = 0;
+    CU(cudaMalloc((void**)&c->d_input, bytes));
+    c->d_input_cap = bytes;
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContext** out_ctx) {
+    if (!out_ctx) return make_error(XETGPU_ERR_INVALID_CONFIG, "out_ctx is NULL");
+    *out_ctx = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return make_error(XETGPU_ERR_UNKNOWN, "no CUDA device available (libxetgpu has no CPU path)",
+                          e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    int dev = config ? config->device : -1;
+    if (dev < 0) CU(cudaGetDevice(&dev));
+    if (dev >= ndev) return make_error(XETGPU_ERR_INVALID_CONFIG, "device ordinal out of range");
+    CU(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10)
+        return make_error(XETGPU_ERR_UNKNOWN, "libxetgpu is built for sm_100a (B200) only", prop.name);
+    XetGpuContext* c = new XetGpuContext();
+    c->device = dev;
+    if (config) {
+        c->flags = config->flags;
+        if (config->staging_bytes) c->staging_bytes = (config->staging_bytes + 4095) & ~4095ull;
+        if (config->max_batch_bytes) c->max_batch_bytes = config->max_batch_bytes;
+        c->stream = (cudaStream_t)config->stream;
+    }
+    if (!c->stream) {
+        cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (se != cudaSuccess) {
+            delete c;
+            return cuda_error(se, "cudaStreamCreateWithFlags");
+        }
+        c->own_stream = true;
+    }
+    for (auto& ev : c->ev) cudaEventCreate(&ev);
+    for (auto& ev : c->stage_free) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    init_gear_kernels();
+    init_chunk_hash_kernels();
+    cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) {
+        delete c;
+        return cuda_error(le, "kernel attribute setup");
+    }
+    *out_ctx = c;
+    return nullptr;
+}
+
+extern "C" void xetgpu_context_free(XetGpuContext* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->ws.base) cudaFree(c->ws.base);
+    if (c->d_input) cudaFree(c->d_input);
+    for (auto& p : c->h_stage)
+        if (p) cudaFreeHost(p);
+    if (c->h_meta) cudaFreeHost(c->h_meta);
+    for (auto& ev : c->ev)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->stage_free)
+        if (ev) cudaEventDestroy(ev);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" XetError* xetgpu_context_set_progress_callback(XetGpuContext* c, XetProgressCallback callback,
+                                                          void* user_data, uint32_t throttle_ms) {
+    if (!c) return make_error(XETGPU_ERR_INVALID_CONFIG, "ctx is NULL");
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->progress = callback;
+    c->progress_user = user_data;
+    c->throttle_ms = throttle_ms;
+    return nullptr;
+}
+
+static void report_progress(XetGpuContext* c, const XetProgressUpdate& u, bool force) {
+    if (!c->progress) return;
+    auto now = std::chrono::steady_clock::now();
+    if (!force && c->throttle_ms &&
+        std::chrono::duration_cast<std::chrono::milliseconds>(now - c->last_progress).count() < c->throttle_ms)
+        return;
+    c->last_progress = now;
+    c->progress(&u, c->progress_user);
+}
+
+// --------------------------------------------------------------------------------- hex helpers
+extern "C" void xetgpu_hash_to_hex(const uint8_t hash[32], char out_hex[65]) {
+    static const char* d = "0123456789abcdef";
+    for (int w = 0; w < 4; w++)
+        for (int b = 0; b < 8; b++) {
+            uint8_t v = hash[8 * w + (7 - b)];  // LE u64 word printed most-significant byte first
+            out_hex[16 * w + 2 * b] = d[v >> 4];
+            out_hex[16 * w + 2 * b + 1] = d[v & 15];
+        }
+    out_hex[64] = 0;
+}
+
+extern "C" XetError* xetgpu_hash_from_hex(const char* hex, uint8_t out_hash[32]) {
+    if (!hex || !out_hash) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument");
+    if (strlen(hex) != 64) return make_error(XETGPU_ERR_INVALID_CONFIG, "a Xet hash is 64 hex digits", hex);
+    for (int w = 0; w < 4; w++)
+        for (int b = 0; b < 8; b++) {
+            int v = 0;
+            for (int k = 0; k < 2; k++) {
+                char ch = hex[16 * w + 2 * b + k];
+                int x = (ch >= '0' && ch <= '9')   ? ch - '0'
+                        : (ch >= 'a' && ch <= 'f') ? ch - 'a' + 10
+                        : (ch >= 'A' && ch <= 'F') ? ch - 'A' + 10
+                                                   : -1;
+                if (x < 0) return make_error(XETGPU_ERR_INVALID_CONFIG, "invalid hex digit in Xet hash", hex);
+                v = v * 16 + x;
+            }
+            out_hash[8 * w + (7 - b)] = (uint8_t)v;
+        }
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------------- workspace
+struct Plan {
+    uint64_t total = 0;
+    uint32_t n_files = 0;
+    uint64_t n_slots = 0;
+    uint32_t n_tiles = 0;
+    uint64_t n_groups_cap = 0;
+    uint64_t cand_cap = 0;
+    uint32_t max_levels = 0;
+    std::vector<uint64_t> slot_off;  // host prefix
+};
+
+static uint32_t bit_length(uint64_t v) {
+    uint32_t n = 0;
+    while (v) {
+        n++;
+        v >>= 1;
+    }
+    return n;
+}
+
+static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, uint64_t cand_cap_hint) {
+    Plan p;
+    p.total = total;
+    p.n_files = (uint32_t)n_files;
+    p.slot_off.resize(n_files + 1);
+    uint64_t s = 0, max_slots = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        p.slot_off[f] = s;
+        uint64_t len = offsets[f + 1] - offsets[f];
+        uint64_t ub = len / kMinChunk + 2;  // every chunk but the last is >= 8192 bytes (+1 sentinel slot)
+        max_slots = std::max(max_slots, ub);
+        s += ub;
+    }
+    p.slot_off[n_files] = s;
+    p.n_slots = s;
+    p.n_tiles = (uint32_t)((total + kGearTile - 1) / kGearTile);
+    p.n_groups_cap = total / (kLeavesPerGroup * 1024ull) + s;
+    p.cand_cap = std::max<uint64_t>(std::max<uint64_t>(total / 1024 + 4096, cand_cap_hint), 1);
+    p.max_levels = bit_length(max_slots) + 1;
+    return p;
+}
+
+static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool dry, uint64_t* need) {
+    Arena a = c->ws;
+    a.used = 0;
+    if (dry) a.base = nullptr;
+    const uint64_t F = p.n_files, S = p.n_slots, T = p.n_tiles;
+    b->n_files = p.n_files;
+    b->n_slots = S;
+    b->n_tiles = p.n_tiles;
+    b->n_groups_cap = p.n_groups_cap;
+    b->cand_cap = p.cand_cap;
+    b->max_levels = p.max_levels;
+    b->total_bytes = p.total;
+    b->file_off = a.take<uint64_t>(F + 1);
+    b->slot_off = a.take<uint64_t>(F + 1);
+    b->tile_count = a.take<uint32_t>(T + 1);
+    b->tile_stage = a.take<uint32_t>(T * (uint64_t)kGearCap + 1);
+    b->tile_off = a.take<uint64_t>(T + 2);
+    b->cand = a.take<uint64_t>(p.cand_cap);
+    b->slot_end = a.take<uint64_t>(S + 1);
+    b->file_count = a.take<uint32_t>(F + 1);
+    b->first_start = a.take<uint64_t>(F + 1);
+    b->file_chunk_base = a.take<uint64_t>(F + 2);
+    b->chunk_start = a.take<uint64_t>(S + 1);
+    b->chunk_len = a.take<uint32_t>(S + 1);
+    b->chunk_file = a.take<uint32_t>(S + 1);
+    b->slot_groups = a.take<uint32_t>(S + 1);
+    b->group_off = a.take<uint64_t>(S + 2);
+    b->group_chunk = a.take<uint32_t>(p.n_groups_cap + 1);
+    b->group_cv = a.take<uint32_t>((p.n_groups_cap + 1) * 8);
+    b->chunk_hash = a.take<uint8_t>((S + 1) * 32);
+    b->node_hash[0] = b->chunk_hash;
+    b->node_hash[1] = a.take<uint8_t>((S + 1) * 32);
+    b->node_size[0] = a.take<uint64_t>(S + 1);
+    b->node_size[1] = a.take<uint64_t>(S + 1);
+    b->level_count[0] = a.take<uint32_t>(F + 1);
+    b->level_count[1] = a.take<uint32_t>(F + 1);
+    b->group_start = a.take<uint32_t>(S + 2);
+    b->file_root = a.take<uint8_t>((F + 1) * 32);
+    b->file_hash = a.take<uint8_t>((F + 1) * 32);
+    b->out_end = a.take<uint64_t>(S + 1);
+    b->out_hash = a.take<uint8_t>((S + 1) * 32);
+    b->scan_partial = a.take<uint64_t>(scan_blocks(std::max<uint64_t>(std::max<uint64_t>(T, S), F) + 2) + 1);
+    b->scalars = a.take<uint64_t>(8);
+    *need = a.used;
+    return nullptr;
+}
+
+static XetError* ensure_workspace(XetGpuContext* c, const Plan& p, PipelineBuffers* b) {
+    uint64_t need = 0;
+    carve(c, p, b, true, &need);
+    if (need > c->ws.cap) {
+        if (c->ws.base) {
+            cudaStreamSynchronize(c->stream);
+            cudaFree(c->ws.base);
+        }
+        c->ws.base = nullptr;
+        c->ws.cap = 0;
+        uint64_t cap = need + need / 8;
+        CU(cudaMalloc((void**)&c->ws.base, cap));
+        c->ws.cap = cap;
+    }
+    return carve(c, p, b, false, &need);
+}
+
+// ---------------------------------------------------------------------------------- ingestion
+// Copy host bytes to the device through the two pinned staging buffers: the CPU fills one buffer
+// while the DMA engine drains the other.  Pinned callers (cudaHostAlloc / cudaHostRegister) are
+// copied directly in staging-sized pieces.
+static XetError* ensure_staging(XetGpuContext* c) {
+    for (int i = 0; i < 2; i++)
+        if (!c->h_stage[i]) CU(cudaMallocHost((void**)&c->h_stage[i], c->staging_bytes));
+    return nullptr;
+}
+
+static bool host_ptr_is_pinned(const void* p) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
+
+static XetError* ingest_host(XetGpuContext* c, const uint8_t* src, uint64_t bytes, uint8_t* d_dst) {
+    if (bytes == 0) return nullptr;
+    if (host_ptr_is_pinned(src)) {
+        for (uint64_t o = 0; o < bytes; o += c->staging_bytes) {
+            uint64_t n = std::min<uint64_t>(c->staging_bytes, bytes - o);
+            CU(cudaMemcpyAsync(d_dst + o, src + o, n, cudaMemcpyHostToDevice, c->stream));
+        }
+        return nullptr;
+    }
+    if (XetError* e = ensure_staging(c)) return e;
+    int i = 0;
+    for (uint64_t o = 0; o < bytes; o += c->staging_bytes, i ^= 1) {
+        uint64_t n = std::min<uint64_t>(c->staging_bytes, bytes - o);
+        CU(cudaEventSynchronize(c->stage_free[i]));  // the copy that last used this buffer has drained
+        memcpy(c->h_stage[i], src + o, n);
+        CU(cudaMemcpyAsync(d_dst + o, c->h_stage[i], n, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaEventRecord(c->stage_free[i], c->stream));
+    }
+    return nullptr;
+}
+
+// ----------------------------------------------------------------------------------- pipeline
+extern "C" void xetgpu_free_result(XetGpuResult* r) {
+    if (!r) return;
+    free(r->files);
+    free(r->chunk_ends);
+    free(r->chunk_hashes);
+    free(r);
+}
+
+extern "C" void xetgpu_free_u64(uint64_t* a) { free(a); }
+
+struct RunOptions {
+    const RangeWalk* range = nullptr;  // byte-range mode (one file)
+    uint64_t end_bias = 0;             // added to every returned chunk end (range mode: file position of data[0])
+    bool want_chunks = false;
+    bool resolve_only = false;         // stop after K2 (range exit-cut query)
+    uint64_t* exit_cut_abs = nullptr;  // resolve_only / range: last cut (absolute in data), or walk_start if none
+    bool skip_merkle = false;
+};
+
+// d_data: device bytes; offsets: host, relative to d_data.
+static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uint64_t* offsets, size_t n_files,
+                              const RunOptions& opt, XetGpuResult** out_result) {
+    const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
+    const uint64_t total = n_files ? offsets[n_files] : 0;
+    for (int attempt = 0; attempt < 3; attempt++) {
+        Plan plan = make_plan(offsets, n_files, total, c->cand_cap_hint);
+        PipelineBuffers b{};
+        if (XetError* e = ensure_workspace(c, plan, &b)) return e;
+        b.data = d_data;
+        // metadata upload through pinned memory
+        const uint64_t F = n_files;
+        const uint64_t meta_bytes = (F + 1) * 16 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
+        if (XetError* e = ensure_meta(c, meta_bytes)) return e;
+        uint64_t* h_off = reinterpret_cast<uint64_t*>(c->h_meta);
+        uint64_t* h_slot = h_off + (F + 1);
+        memcpy(h_off, offsets, (F + 1) * 8);
+        memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
+        cudaStream_t st = c->stream;
+        int launches = 0;
+        if (timing) cudaEventRecord(c->ev[0], st);
+        CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(b.scalars, 0, 64, st));
+        launches += launch_gear(b, st);
+        if (timing) cudaEventRecord(c->ev[1], st);
+        launches += launch_resolve(b, opt.range, st);
+        if (timing) cudaEventRecord(c->ev[2], st);
+        if (!opt.resolve_only) {
+            launches += launch_chunk_hash(b, st);
+            launches += launch_gather(b, st);
+            if (timing) cudaEventRecord(c->ev[3], st);
+            if (!opt.skip_merkle) launches += launch_merkle(b, st);
+            if (timing) cudaEventRecord(c->ev[4], st);
+        } else {
+            launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
+                                        b.scalars + kScalarChunks, st);
+            if (timing) {
+                cudaEventRecord(c->ev[3], st);
+                cudaEventRecord(c->ev[4], st);
+            }
+        }
+        CU(cudaGetLastError());
+        // readback: scalars, per-file counts, bases, roots, hashes
+        uint8_t* h_rb = c->h_meta + (F + 1) * 16;
+        uint64_t* h_scalars = reinterpret_cast<uint64_t*>(h_rb);
+        uint64_t* h_base = h_scalars + 8;
+        uint32_t* h_count = reinterpret_cast<uint32_t*>(h_base + (F + 2));
+        uint8_t* h_hash = reinterpret_cast<uint8_t*>(h_count + (F + 1 + ((F + 1) & 1)));
+        uint8_t* h_root = h_hash + (F + 1) * 32;
+        CU(cudaMemcpyAsync(h_scalars, b.scalars, 64, cudaMemcpyDeviceToHost, st));
+        if (F) {
+            CU(cudaMemcpyAsync(h_base, b.file_chunk_base, (F + 1) * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h_count, b.file_count, F * 4, cudaMemcpyDeviceToHost, st));
+            if (!opt.resolve_only && !opt.skip_merkle) {
+                CU(cudaMemcpyAsync(h_hash, b.file_hash, F * 32, cudaMemcpyDeviceToHost, st));
+                CU(cudaMemcpyAsync(h_root, b.file_root, F * 32, cudaMemcpyDeviceToHost, st));
+            }
+        }
+        if (timing) cudaEventRecord(c->ev[5], st);
+        CU(cudaStreamSynchronize(st));
+        const uint64_t n_cand = h_scalars[kScalarCand];
+        if (n_cand > plan.cand_cap) {  // candidate list overflowed (dense data): grow and redo
+            c->cand_cap_hint = n_cand + n_cand / 8 + 1024;
+            continue;
+        }
+        const uint64_t n_chunks = F ? h_base[F] : 0;
+        if (opt.exit_cut_abs) {
+            uint64_t last = opt.range ? opt.range->walk_start : 0;
+            if (n_chunks) CU(cudaMemcpy(&last, b.slot_end + (plan.slot_off[F - 1] + h_count[F - 1] - 1), 8,
+                                        cudaMemcpyDeviceToHost));
+            *opt.exit_cut_abs = last;
+        }
+        XetGpuResult* r = nullptr;
+        if (out_result) {
+            r = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
+            if (!r) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+            r->n_files = n_files;
+            r->files = (XetGpuFileResult*)calloc(n_files ? n_files : 1, sizeof(XetGpuFileResult));
+            for (size_t f = 0; f < n_files; f++) {
+                XetGpuFileResult& fr = r->files[f];
+                if (!opt.resolve_only && !opt.skip_merkle) {
+                    memcpy(fr.file_hash, h_hash + f * 32, 32);
+                    memcpy(fr.merkle_root, h_root + f * 32, 32);
+                }
+                fr.size = offsets[f + 1] - offsets[f];
+                fr.n_chunks = h_count[f];
+                fr.first_chunk = h_base[f];
+            }
+            if (opt.want_chunks && n_chunks) {
+                r->n_chunks = n_chunks;
+                r->chunk_ends = (uint64_t*)malloc(n_chunks * 8);
+                r->chunk_hashes = (uint8_t*)malloc(n_chunks * 32);
+                if (!r->chunk_ends || !r->chunk_hashes) {
+                    xetgpu_free_result(r);
+                    return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+                }
+                if (opt.resolve_only) {
+                    // ends only: gather was skipped; single file in this mode
+                    CU(cudaMemcpyAsync(r->chunk_ends, b.slot_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+                    memset(r->chunk_hashes, 0, n_chunks * 32);
+                } else {
+                    CU(cudaMemcpyAsync(r->chunk_ends, b.out_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+                    CU(cudaMemcpyAsync(r->chunk_hashes, b.out_hash, n_chunks * 32, cudaMemcpyDeviceToHost, st));
+                }
+                CU(cudaStreamSynchronize(st));
+                if (opt.end_bias)
+                    for (uint64_t i = 0; i < n_chunks; i++) r->chunk_ends[i] += opt.end_bias;
+            }
+            *out_result = r;
+        }
+        if (timing) {
+            cudaEventRecord(c->ev[6], st);
+            cudaEventSynchronize(c->ev[6]);
+            XetGpuTimings& t = c->last;
+            cudaEventElapsedTime(&t.gear_ms, c->ev[0], c->ev[1]);
+            cudaEventElapsedTime(&t.resolve_ms, c->ev[1], c->ev[2]);
+            cudaEventElapsedTime(&t.blake3_ms, c->ev[2], c->ev[3]);
+            cudaEventElapsedTime(&t.merkle_ms, c->ev[3], c->ev[4]);
+            cudaEventElapsedTime(&t.d2h_ms, c->ev[4], c->ev[6]);
+            cudaEventElapsedTime(&t.total_ms, c->ev[0], c->ev[6]);
+        }
+        c->last.bytes = total;
+        c->last.n_chunks = n_chunks;
+        c->last.n_candidates = n_cand;
+        c->last.kernel_launches = (uint32_t)launches;
+        return nullptr;
+    }
+    return make_error(XETGPU_ERR_UNKNOWN, "candidate list kept overflowing");
+}
+
+static XetError* resolve_memory_kind(const void* data, int32_t memory, bool* is_device) {
+    if (memory == XETGPU_MEM_DEVICE) {
+        *is_device = true;
+    } else if (memory == XETGPU_MEM_HOST) {
+        *is_device = false;
+    } else if (memory == XETGPU_MEM_AUTO) {
+        cudaPointerAttributes attr;
+        cudaError_t e = cudaPointerGetAttributes(&attr, data);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            *is_device = false;
+        } else {
+            *is_device = attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+        }
+    } else {
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "memory must be XETGPU_MEM_AUTO, _HOST or _DEVICE");
+    }
+    return nullptr;
+}
+
+// Brings [data+lo, data+hi) onto the device if needed.  Returns a 16-byte aligned device pointer
+// d such that d[0] is data[lo] ... plus the offset shift to apply.
+static XetError* stage_input(XetGpuContext* c, const void* data, uint64_t lo, uint64_t hi, int32_t memory,
+                             const uint8_t** d_out) {
+    bool is_device = false;
+    if (XetError* e = resolve_memory_kind(data, memory, &is_device)) return e;
+    const uint8_t* p = (const uint8_t*)data + lo;
+    const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
+    c->last.h2d_ms = 0.f;
+    if (is_device) {
+        if (((uintptr_t)p & 15u) == 0) {
+            *d_out = p;
+            return nullptr;
+        }
+        // unaligned device input: one device-to-device copy into the aligned input buffer
+        if (XetError* e = ensure_input(c, hi - lo)) return e;
+        CU(cudaMemcpyAsync(c->d_input, p, hi - lo, cudaMemcpyDeviceToDevice, c->stream));
+        *d_out = c->d_input;
+        return nullptr;
+    }
+    if (XetError* e = ensure_input(c, hi - lo)) return e;
+    if (timing) cudaEventRecord(c->ev[7], c->stream);
+    if (XetError* e = ingest_host(c, p, hi - lo, c->d_input)) return e;
+    if (timing) {
+        cudaEventRecord(c->ev[6], c->stream);
+        cudaEventSynchronize(c->ev[6]);
+        cudaEventElapsedTime(&c->last.h2d_ms, c->ev[7], c->ev[6]);
+    }
+    *d_out = c->d_input;
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, const uint64_t* offsets,
+                                         size_t n_files, int32_t memory, uint32_t flags,
+                                         XetGpuResult** out_result) {
+    if (!c || !out_result || (n_files && !offsets))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_hash_buffers");
+    *out_result = nullptr;
+    for (size_t f = 0; f < n_files; f++)
+        if (offsets[f + 1] < offsets[f])
+            return make_error(XETGPU_ERR_INVALID_CONFIG, "offsets must be ascending");
+    if (n_files && offsets[n_files] > offsets[0] && !data)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    std::vector<uint64_t> rel(n_files + 1, 0);
+    const uint64_t lo = n_files ? offsets[0] : 0;
+    for (size_t f = 0; f <= n_files && n_files; f++) rel[f] = offsets[f] - lo;
+    const uint8_t* d = nullptr;
+    if (n_files && rel[n_files])
+        if (XetError* e = stage_input(c, data, lo, offsets[n_files], memory, &d)) return e;
+    RunOptions opt;
+    opt.want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
+    return run_pipeline(c, d, rel.data(), n_files, opt, out_result);
+}
+
+// -------------------------------------------------------------------------------------- files
+static XetError* read_fully(int fd, uint8_t* dst, uint64_t n, const char* path) {
+    uint64_t got = 0;
+    while (got < n) {
+        ssize_t r = read(fd, dst + got, n - got);
+        if (r < 0) {
+            if (errno == EINTR) continue;
+            return make_error(XETGPU_ERR_IO, std::string("read failed: ") + strerror(errno), path);
+        }
+        if (r == 0) return make_error(XETGPU_ERR_IO, "file shrank while being read", path);
+        got += (uint64_t)r;
+    }
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* paths, size_t n_files, uint32_t flags,
+                                       const XetCancellationToken* cancel, XetGpuResult** out_result) {
+    if (!c || !out_result || (n_files && !paths))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_hash_files");
+    *out_result = nullptr;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (XetError* e = ensure_staging(c)) return e;
+    std::vector<uint64_t> sizes(n_files);
+    uint64_t all_bytes = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
+        struct stat st;
+        if (stat(paths[f], &st) != 0)
+            return make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
+                              std::string("cannot stat file: ") + strerror(errno), paths[f]);
+        if (!S_ISREG(st.st_mode)) return make_error(XETGPU_ERR_IO, "not a regular file", paths[f]);
+        sizes[f] = (uint64_t)st.st_size;
+        all_bytes += sizes[f];
+    }
+    const bool want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
+    XetGpuResult* total = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
+    total->n_files = n_files;
+    total->files = (XetGpuFileResult*)calloc(n_files ? n_files : 1, sizeof(XetGpuFileResult));
+    std::vector<uint64_t> all_ends;
+    std::vector<uint8_t> all_hashes;
+    XetProgressUpdate pu{};
+    pu.phase = XET_PROGRESS_PHASE_SCANNING;
+    pu.total_bytes = all_bytes;
+    pu.total_files = (uint32_t)n_files;
+    XetError* err = nullptr;
+    size_t f0 = 0;
+    while (f0 < n_files && !err) {
+        // batch = as many whole files as fit in max_batch_bytes (at least one)
+        size_t f1 = f0;
+        uint64_t bytes = 0;
+        while (f1 < n_files && (f1 == f0 || bytes + sizes[f1] <= c->max_batch_bytes)) bytes += sizes[f1++];
+        if ((err = ensure_input(c, bytes))) break;
+        std::vector<uint64_t> rel(f1 - f0 + 1, 0);
+        uint64_t dev_off = 0;
+        int buf = 0;
+        for (size_t f = f0; f < f1 && !err; f++) {
+            if (cancel && cancel->callback && cancel->callback(cancel->user_data)) {
+                err = make_error(XETGPU_ERR_CANCELLED, "cancelled");
+                break;
+            }
+            rel[f - f0] = dev_off;
+            int fd = open(paths[f], O_RDONLY);
+            if (fd < 0) {
+                err = make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
+                                 std::string("cannot open file: ") + strerror(errno), paths[f]);
+                break;
+            }
+            pu.current_file = paths[f];
+            pu.current_file_total_bytes = sizes[f];
+            for (uint64_t o = 0; o < sizes[f] && !err; o += c->staging_bytes, buf ^= 1) {
+                uint64_t n = std::min<uint64_t>(c->staging_bytes, sizes[f] - o);
+                cudaEventSynchronize(c->stage_free[buf]);
+                if ((err = read_fully(fd, c->h_stage[buf], n, paths[f]))) break;
+                cudaError_t ce = cudaMemcpyAsync(c->d_input + dev_off + o, c->h_stage[buf], n, cudaMemcpyHostToDevice,
+                                                 c->stream);
+                if (ce != cudaSuccess) {
+                    err = cuda_error(ce, "cudaMemcpyAsync(H2D)");
+                    break;
+                }
+                cudaEventRecord(c->stage_free[buf], c->stream);
+                pu.completed_bytes += n;
+                pu.current_file_completed_bytes = o + n;
+                report_progress(c, pu, false);
+            }
+            close(fd);
+            dev_off += sizes[f];
+            pu.completed_files++;
+        }
+        if (err) break;
+        rel[f1 - f0] = dev_off;
+        RunOptions opt;
+        opt.want_chunks = want_chunks;
+        XetGpuResult* part = nullptr;
+        if ((err = run_pipeline(c, c->d_input, rel.data(), f1 - f0, opt, &part))) break;
+        for (size_t f = f0; f < f1; f++) {
+            total->files[f] = part->files[f - f0];
+            total->files[f].first_chunk += all_ends.size();
+        }
+        if (want_chunks && part->n_chunks) {
+            all_ends.insert(all_ends.end(), part->chunk_ends, part->chunk_ends + part->n_chunks);
+            all_hashes.insert(all_hashes.end(), part->chunk_hashes, part->chunk_hashes + part->n_chunks * 32);
+        }
+        xetgpu_free_result(part);
+        f0 = f1;
+    }
+    if (err) {
+        cudaStreamSynchronize(c->stream);
+        xetgpu_free_result(total);
+        return err;
+    }
+    if (want_chunks && !all_ends.empty()) {
+        total->n_chunks = all_ends.size();
+        total->chunk_ends = (uint64_t*)malloc(all_ends.size() * 8);
+        total->chunk_hashes = (uint8_t*)malloc(all_hashes.size());
+        memcpy(total->chunk_ends, all_ends.data(), all_ends.size() * 8);
+        memcpy(total->chunk_hashes, all_hashes.data(), all_hashes.size());
+    }
+    pu.phase = XET_PROGRESS_PHASE_FINALIZING;
+    pu.current_file = nullptr;
+    report_progress(c, pu, true);
+    *out_result = total;
+    return nullptr;
+}
+
+// ------------------------------------------------------------------------------------- verify
+static XetError* compare_hash(const uint8_t got[32], const char* expected_hex, const char* what) {
+    uint8_t want[32];
+    if (XetError* e = xetgpu_hash_from_hex(expected_hex, want)) return e;
+    if (memcmp(got, want, 32) == 0) return nullptr;
+    char hex[65];
+    xetgpu_hash_to_hex(got, hex);
+    return make_error(XETGPU_ERR_CHECKSUM_MISMATCH, std::string("xet hash mismatch for ") + what,
+                      std::string("expected ") + expected_hex + " computed " + hex);
+}
+
+extern "C" XetError* xetgpu_verify_file(XetGpuContext* c, const char* path, const char* expected_hex) {
+    if (!c || !path || !expected_hex) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_verify_file");
+    uint8_t want[32];
+    if (XetError* e = xetgpu_hash_from_hex(expected_hex, want)) return e;
+    XetGpuResult* r = nullptr;
+    const char* paths[1] = {path};
+    if (XetError* e = xetgpu_hash_files(c, paths, 1, 0, nullptr, &r)) return e;
+    XetError* e = compare_hash(r->files[0].file_hash, expected_hex, path);
+    xetgpu_free_result(r);
+    return e;
+}
+
+extern "C" XetError* xetgpu_verify_buffer(XetGpuContext* c, const void* data, uint64_t len, int32_t memory,
+                                          const char* expected_hex) {
+    if (!c || !expected_hex || (len && !data))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_verify_buffer");
+    uint8_t want[32];
+    if (XetError* e = xetgpu_hash_from_hex(expected_hex, want)) return e;
+    XetGpuResult* r = nullptr;
+    uint64_t offsets[2] = {0, len};
+    if (XetError* e = xetgpu_hash_buffers(c, data, offsets, 1, memory, 0, &r)) return e;
+    XetError* e = compare_hash(r->files[0].file_hash, expected_hex, "buffer");
+    xetgpu_free_result(r);
+    return e;
+}
+
+// ------------------------------------------------------------------------- stage-level entries
+extern "C" XetError* xetgpu_gear_candidates(XetGpuContext* c, const void* data, uint64_t len, int32_t memory,
+                                            uint64_t** out_indices, uint64_t* out_count) {
+    if (!c || !out_indices || !out_count || (len && !data))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_gear_candidates");
+    *out_indices = nullptr;
+    *out_count = 0;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (len == 0) return nullptr;
+    const uint8_t* d = nullptr;
+    if (XetError* e = stage_input(c, data, 0, len, memory, &d)) return e;
+    uint64_t offsets[2] = {0, len};
+    for (int attempt = 0; attempt < 3; attempt++) {
+        Plan plan = make_plan(offsets, 1, len, c->cand_cap_hint);
+        PipelineBuffers b{};
+        if (XetError* e = ensure_workspace(c, plan, &b)) return e;
+        b.data = d;
+        CU(cudaMemsetAsync(b.scalars, 0, 64, c->stream));
+        launch_gear(b, c->stream);
+        CU(cudaGetLastError());
+        uint64_t n = 0;
+        CU(cudaMemcpyAsync(&n, b.scalars + kScalarCand, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (n > plan.cand_cap) {
+            c->cand_cap_hint = n + n / 8 + 1024;
+            continue;
+        }
+        uint64_t* out = (uint64_t*)malloc((n ? n : 1) * 8);
+        if (!out) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+        if (n) CU(cudaMemcpy(out, b.cand, n * 8, cudaMemcpyDeviceToHost));
+        *out_indices = out;
+        *out_count = n;
+        return nullptr;
+    }
+    return make_error(XETGPU_ERR_UNKNOWN, "candidate list kept overflowing");
+}
+
+static XetError* range_common(XetGpuContext* c, const void* data, int32_t memory, uint64_t file_len,
+                              uint64_t range_begin, uint64_t range_end, uint64_t entry_cut, bool resolve_only,
+                              uint64_t* out_exit_cut, XetGpuResult** out_result) {
+    if (!c || !out_exit_cut) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to range call");
+    if (range_begin > range_end || range_end > file_len || entry_cut > range_begin)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "need entry_cut <= range_begin <= range_end <= file_len");
+    const uint64_t lead = std::min<uint64_t>(range_begin, XETGPU_RANGE_LEAD);
+    const uint64_t data_pos = range_begin - lead;  // file position of data[0]
+    if (entry_cut < data_pos || range_begin - entry_cut > XETGPU_MAX_CHUNK)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "entry_cut must lie within one maximum chunk before range_begin");
+    if (out_result) *out_result = nullptr;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const uint64_t len = range_end - data_pos;
+    if (len && !data) return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
+    const uint8_t* d = nullptr;
+    if (len)
+        if (XetError* e = stage_input(c, data, 0, len, memory, &d)) return e;
+    uint64_t offsets[2] = {0, len};
+    RangeWalk rw{entry_cut - data_pos, range_end == file_len ? 1u : 0u};
+    RunOptions opt;
+    opt.range = &rw;
+    opt.end_bias = data_pos;
+    opt.want_chunks = !resolve_only;
+    opt.resolve_only = resolve_only;
+    opt.skip_merkle = true;
+    uint64_t exit_abs = 0;
+    opt.exit_cut_abs = &exit_abs;
+    if (XetError* e = run_pipeline(c, d, offsets, 1, opt, out_result)) return e;
+    *out_exit_cut = exit_abs + data_pos;
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_hash_range(XetGpuContext* c, const void* data, int32_t memory, uint64_t file_len,
+                                       uint64_t range_begin, uint64_t range_end, uint64_t entry_cut,
+                                       uint64_t* out_exit_cut, XetGpuResult** out_result) {
+    if (!out_result) return make_error(XETGPU_ERR_INVALID_CONFIG, "out_result is NULL");
+    return range_common(c, data, memory, file_len, range_begin, range_end, entry_cut, false, out_exit_cut, out_result);
+}
+
+extern "C" XetError* xetgpu_range_exit_cut(XetGpuContext* c, const void* data, int32_t memory, uint64_t file_len,
+                                           uint64_t range_begin, uint64_t range_end, uint64_t entry_cut,
+                                           uint64_t* out_exit_cut) {
+    return range_common(c, data, memory, file_len, range_begin, range_end, entry_cut, true, out_exit_cut, nullptr);
+}
+
+extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* chunk_hashes,
+                                               const uint64_t* chunk_sizes, uint64_t n_chunks,
+                                               uint8_t out_merkle_root[32], uint8_t out_file_hash[32]) {
+    if (!c || !out_merkle_root || !out_file_hash || (n_chunks && (!chunk_hashes || !chunk_sizes)))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_merkle_from_chunks");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    // a one-file plan whose slot range holds exactly n_chunks nodes
+    Plan plan;
+    plan.total = 0;
+    plan.n_files = 1;
+    plan.slot_off = {0, n_chunks + 1};
+    plan.n_slots = n_chunks + 1;
+    plan.n_tiles = 0;
+    plan.n_groups_cap = 1;
+    plan.cand_cap = 1;
+    plan.max_levels = bit_length(n_chunks + 1) + 1;
+    PipelineBuffers b{};
+    if (XetError* e = ensure_workspace(c, plan, &b)) return e;
+    cudaStream_t st = c->stream;
+    uint64_t h_slot[2] = {0, n_chunks + 1};
+    uint32_t cnt = (uint32_t)n_chunks;
+    CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(b.file_count, &cnt, 4, cudaMemcpyHostToDevice, st));
+    if (n_chunks) {
+        CU(cudaMemcpyAsync(b.chunk_hash, chunk_hashes, n_chunks * 32, cudaMemcpyHostToDevice, st));
+        // sizes may exceed 32 bits here (callers combine arbitrary (hash, size) lists): upload u64
+        // sizes straight into the level-0 size array and skip the u32 chunk_len initialisation
+        CU(cudaMemcpyAsync(b.node_size[0], chunk_sizes, n_chunks * 8, cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaStreamSynchronize(st));  // the host sources above are pageable stack/heap memory
+    PipelineBuffers m = b;
+    m.chunk_len = nullptr;  // launch_merkle: sizes already in place
+    launch_merkle(m, st);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out_merkle_root, b.file_root, 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_file_hash, b.file_hash, 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_fill_splitmix(XetGpuContext* c, void* device_dst, uint64_t seed, uint64_t byte_off,
+                                          uint64_t len) {
+    if (!c || (len && !device_dst)) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_fill_splitmix");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    launch_fill_splitmix((uint8_t*)device_dst, seed, byte_off, len, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_last_timings(XetGpuContext* c, XetGpuTimings* out) {
+    if (!c || !out) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_last_timings");
+    std::lock_guard<std::mutex> lk(c->mu);
+    *out = c->last;
+    return nullptr;
+}

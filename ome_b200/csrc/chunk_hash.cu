@@ -1,0 +1,210 @@
+// K3: keyed-BLAKE3 chunk hashes (merklehash::compute_data_hash = blake3::keyed_hash(DATA_KEY, chunk);
+// xet-core merklehash 0.14.5 pinned at /root/reference pkg/xet/Cargo.lock:1651-1663; the reference's
+// only direct call site is pkg/xet/src/xet_downloader.rs:217).
+//
+// Work decomposition.  BLAKE3 splits a chunk into 1 KiB leaves whose chaining values are merged
+// by a left-heavy binary tree.  Leaf positions are relative to the (data-dependent) chunk start,
+// so the work list is built after K2: a *group* is up to four consecutive leaves of one chunk,
+// aligned at a multiple of four leaves from the chunk start, i.e. a complete subtree.  One lane
+// hashes one group: 16 serial compressions per leaf with the whole state in registers, then the
+// 2-level subtree merge in registers.  All 32 lanes of a warp do identical work except at chunk
+// tails.  The few remaining tree levels (<= 32 group values per chunk) are folded by K3b.
+//
+// Data movement.  A lane's leaf is 1 KiB at an arbitrary byte address.  Before each leaf round
+// every lane issues ONE bulk TMA copy (cp.async.bulk -> UBLKCP) of the 16-byte-aligned span that
+// covers its leaf into its own 1040-byte row of the warp's shared-memory stage; completion is
+// signalled on a per-warp mbarrier.  No LSU instruction is spent on staging and HBM lines are
+// read once.  Message words are then read with LDS.32 from the row (row stride 1040 B: lanes
+// l, l+8, l+16, l+24 share a bank — a 4-way conflict that costs 68 of the ~1400 issue cycles of a
+// compression) and realigned with one funnel shift per word for the chunk's byte offset.
+#include "blake3_dev.cuh"
+#include "tma.cuh"
+#include "xetgpu_internal.h"
+
+namespace xetgpu {
+
+int launch_chunk_bookkeeping(const PipelineBuffers& b, cudaStream_t st);  // resolve.cu
+
+
+constexpr int kLeafThreads = kLeafWarpsPerCta * 32;
+constexpr int kLeafStage = 32 * kLeafRow;                       // bytes of shared memory per warp
+constexpr int kLeafSmem = kLeafWarpsPerCta * kLeafStage;
+
+// Hash one staged leaf (<= 1024 bytes, at byte `off` of the lane's row) into `cv`.
+__device__ __forceinline__ void hash_leaf(const uint32_t* __restrict__ row, uint32_t off, uint32_t leaf_len,
+                                          uint32_t leaf_index, bool active, bool root_leaf, const uint32_t (&key)[8],
+                                          uint32_t (&cv)[8]) {
+    const uint32_t nb = leaf_len <= 64 ? 1u : (leaf_len + 63u) / 64u;
+    const uint32_t shift = (off & 3u) * 8u;
+    const uint32_t* wrow = row + (off >> 2);
+#pragma unroll
+    for (int i = 0; i < 8; i++) cv[i] = key[i];
+#pragma unroll 1
+    for (uint32_t b = 0; b < 16; b++) {
+        const bool go = active && b < nb;
+        if (!__any_sync(0xffffffffu, go)) break;
+        if (go) {
+            uint32_t w[17];
+#pragma unroll
+            for (int i = 0; i < 17; i++) w[i] = wrow[b * 16 + i];
+            uint32_t m[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) m[i] = __funnelshift_r(w[i], w[i + 1], shift);
+            uint32_t bl = 64;
+            if (b == nb - 1) {
+                bl = leaf_len - b * 64;  // 0..64 (0 only for an empty input, which K2 never emits)
+                if (bl < 64) {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) {
+                        const int lo = 4 * i;
+                        if (bl <= (uint32_t)lo) m[i] = 0u;
+                        else if (bl < (uint32_t)lo + 4u) m[i] &= (1u << (8u * (bl - lo))) - 1u;
+                    }
+                }
+            }
+            uint32_t flags = B3_KEYED_HASH;
+            if (b == 0) flags |= B3_CHUNK_START;
+            if (b == nb - 1) flags |= B3_CHUNK_END | (root_leaf ? B3_ROOT : 0u);
+            b3_compress(cv, m, leaf_index, 0u, bl, flags);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kLeafThreads)
+    leaf_group_kernel(const uint8_t* __restrict__ data, const uint64_t* __restrict__ scalars,
+                      const uint32_t* __restrict__ group_chunk, const uint64_t* __restrict__ group_off,
+                      const uint64_t* __restrict__ chunk_start, const uint32_t* __restrict__ chunk_len,
+                      uint32_t* __restrict__ group_cv, uint8_t* __restrict__ chunk_hash) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t s_bar[kLeafWarpsPerCta];
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint64_t n_groups = scalars[kScalarGroups];
+    const uint64_t g = ((uint64_t)blockIdx.x * kLeafWarpsPerCta + wid) * 32u + lane;
+    if (g - lane >= n_groups) return;  // whole warp out of range (warps never sync with each other)
+
+    uint64_t* bar = &s_bar[wid];
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    uint8_t* stage = smem + wid * kLeafStage;
+    uint8_t* my_row = stage + lane * kLeafRow;
+
+    const bool valid = g < n_groups;
+    uint32_t slot = 0, clen = 0, goff = 0, glen = 0, gleaves = 0, cleaves = 0;
+    uint64_t cstart = 0;
+    if (valid) {
+        slot = group_chunk[g];
+        const uint32_t j = (uint32_t)(g - group_off[slot]);
+        cstart = chunk_start[slot];
+        clen = chunk_len[slot];
+        cleaves = clen <= 1024u ? 1u : (clen + 1023u) / 1024u;
+        goff = j * (kLeavesPerGroup * 1024u);
+        glen = clen - goff < kLeavesPerGroup * 1024u ? clen - goff : kLeavesPerGroup * 1024u;
+        gleaves = glen <= 1024u ? 1u : (glen + 1023u) / 1024u;
+    }
+    const uint32_t key[8] = XG_DATA_KEY_WORDS;
+    uint32_t a[8], bq[8], cv[8];
+    uint32_t parity = 0;
+
+#pragma unroll 1
+    for (uint32_t li = 0; li < kLeavesPerGroup; li++) {
+        const bool active = valid && li < gleaves;
+        if (!__any_sync(0xffffffffu, active)) break;
+        const uint64_t src = cstart + goff + li * 1024u;
+        const uint32_t llen = active ? (glen - li * 1024u < 1024u ? glen - li * 1024u : 1024u) : 0u;
+        const uint32_t off = (uint32_t)(src & 15u);
+        const uint32_t copy = active ? ((off + llen + 15u) & ~15u) : 0u;
+        // stage this round's 32 leaves: one bulk copy per lane, one mbarrier phase per round
+        const uint32_t tx = __reduce_add_sync(0xffffffffu, copy);
+        if (lane == 0) mbar_arrive_expect_tx(bar, tx);
+        __syncwarp();
+        if (copy) tma_bulk_g2s(my_row, data + (src - off), copy, bar);
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+
+        hash_leaf(reinterpret_cast<const uint32_t*>(my_row), off, llen, goff / 1024u + li, active,
+                  /*root_leaf=*/cleaves == 1u, key, cv);
+        __syncwarp();  // all lanes are done reading the stage before the next round overwrites it
+
+        if (active) {
+            if (li == 0) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) a[i] = cv[i];
+            } else if (li == 1) {
+                uint32_t l[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) l[i] = a[i];
+                b3_parent(key, l, cv, /*root=*/cleaves == 2u, a);
+            } else if (li == 2) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) bq[i] = cv[i];
+            } else {
+                uint32_t l[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) l[i] = bq[i];
+                b3_parent(key, l, cv, false, bq);
+            }
+        }
+    }
+    if (!valid) return;
+    if (gleaves >= 3) {
+        uint32_t l[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) l[i] = a[i];
+        b3_parent(key, l, bq, /*root=*/cleaves <= (uint32_t)kLeavesPerGroup, a);
+    }
+    uint4* dst = cleaves <= (uint32_t)kLeavesPerGroup ? reinterpret_cast<uint4*>(chunk_hash + (uint64_t)slot * 32)
+                                                       : reinterpret_cast<uint4*>(group_cv + g * 8);
+    dst[0] = make_uint4(a[0], a[1], a[2], a[3]);
+    dst[1] = make_uint4(a[4], a[5], a[6], a[7]);
+}
+
+// K3b: fold a chunk's group values (complete 4-leaf subtrees, the last possibly partial) into the
+// chunk hash.  Pairing neighbours level by level and promoting an odd tail unchanged reproduces
+// BLAKE3's left-heavy tree.  One thread per chunk; <= 31 compressions.
+__global__ void chunk_tree_kernel(uint64_t n_slots, const uint32_t* __restrict__ slot_groups,
+                                  const uint64_t* __restrict__ group_off, uint32_t* __restrict__ group_cv,
+                                  uint8_t* __restrict__ chunk_hash) {
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    const uint32_t ng = slot_groups[s];
+    if (ng <= 1) return;  // single-group chunks were finalised by the leaf kernel
+    const uint32_t key[8] = XG_DATA_KEY_WORDS;
+    uint4* cvs = reinterpret_cast<uint4*>(group_cv + group_off[s] * 8);
+    for (uint32_t stride = 1; stride < ng; stride <<= 1) {
+        const bool last = stride * 2 >= ng;
+        for (uint32_t i = 0; i + stride < ng; i += 2 * stride) {
+            uint4 l0 = cvs[2 * i], l1 = cvs[2 * i + 1];
+            uint4 r0 = cvs[2 * (i + stride)], r1 = cvs[2 * (i + stride) + 1];
+            uint32_t l[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+            uint32_t r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            uint32_t o[8];
+            b3_parent(key, l, r, last, o);
+            cvs[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
+            cvs[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(chunk_hash + s * 32);
+    dst[0] = cvs[0];
+    dst[1] = cvs[1];
+}
+
+void init_chunk_hash_kernels() {
+    cudaFuncSetAttribute(leaf_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLeafSmem);
+}
+
+int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st) {
+    int n = launch_chunk_bookkeeping(b, st);
+    if (b.n_slots == 0 || b.n_groups_cap == 0) return n;
+    const uint64_t warps = (b.n_groups_cap + 31) / 32;
+    const unsigned blocks = (unsigned)((warps + kLeafWarpsPerCta - 1) / kLeafWarpsPerCta);
+    leaf_group_kernel<<<blocks, kLeafThreads, kLeafSmem, st>>>(b.data, b.scalars, b.group_chunk, b.group_off,
+                                                               b.chunk_start, b.chunk_len, b.group_cv, b.chunk_hash);
+    chunk_tree_kernel<<<(unsigned)((b.n_slots + 127) / 128), 128, 0, st>>>(b.n_slots, b.slot_groups, b.group_off,
+                                                                          b.group_cv, b.chunk_hash);
+    return n + 2;
+}
+
+}  // namespace xetgpu

@@ -1,0 +1,97 @@
+// Internal declarations shared by the kernel translation units and the C-ABI layer.
+// Not installed; the public surface is include/xetgpu.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace xetgpu {
+
+// ---- chunking constants (xet-core deduplication crate)
+constexpr uint32_t kMinChunk = 8192;
+constexpr uint32_t kMaxChunk = 131072;
+constexpr uint32_t kTopBits = 16;  // MASK = 0xFFFF000000000000: the 16 top bits must be clear
+
+// ---- K1 geometry.  One CTA owns a tile of kGearThreads strips of kGearStrip bytes.  The strip
+// length is an ODD multiple of 16 bytes so that the 32 lanes of a warp, each reading 16 bytes of
+// its own strip, touch 32 distinct 16-byte bank groups (conflict-free LDS.128).
+constexpr int kGearThreads = 128;
+constexpr int kGearStrip = 528;                                 // 33 * 16
+constexpr int kGearTile = kGearThreads * kGearStrip;            // 67,584 bytes
+constexpr int kGearHalo = 64;                                   // bytes staged in front of the tile
+constexpr int kGearCap = 128;                                   // staged candidates per tile (fast path)
+constexpr int kGearTableCopies = 16;                            // smem replicas of the gear table
+
+// ---- K3 geometry.  A "group" is up to kLeavesPerGroup consecutive 1 KiB BLAKE3 leaves of one
+// chunk, hashed by one lane, which also merges them into one subtree chaining value.
+constexpr int kLeavesPerGroup = 4;
+constexpr int kLeafRow = 1040;     // smem bytes per staged leaf: 1024 + 16 (alignment slack); 65*16
+constexpr int kLeafWarpsPerCta = 2;
+
+struct PipelineBuffers {
+    // inputs
+    const uint8_t* data;        // device, 16-byte aligned
+    uint64_t total_bytes;       // bytes addressable from data
+    const uint64_t* file_off;   // device [n_files+1], offsets into data
+    uint32_t n_files;
+    // K1
+    uint32_t n_tiles;
+    uint32_t* tile_count;       // [n_tiles]
+    uint32_t* tile_stage;       // [n_tiles * kGearCap] tile-relative positions
+    uint64_t* tile_off;         // [n_tiles+1] exclusive scan of tile_count
+    uint64_t* cand;             // [cand_cap] absolute candidate byte indices, ascending
+    uint64_t cand_cap;
+    // K2
+    const uint64_t* slot_off;   // device [n_files+1], host-computed prefix of per-file chunk upper bounds
+    uint64_t n_slots;
+    uint64_t* slot_end;         // [n_slots] absolute exclusive end offset of chunk in slot
+    uint32_t* file_count;       // [n_files] chunks per file
+    uint64_t* first_start;      // [n_files] absolute start of the first emitted chunk
+    uint64_t* file_chunk_base;  // [n_files+1] exclusive scan of file_count
+    // K3
+    uint64_t* chunk_start;      // [n_slots] absolute start
+    uint32_t* chunk_len;        // [n_slots] 0 = empty slot
+    uint32_t* chunk_file;       // [n_slots]
+    uint32_t* slot_groups;      // [n_slots] groups per chunk
+    uint64_t* group_off;        // [n_slots+1]
+    uint32_t* group_chunk;      // [n_groups_cap]
+    uint64_t n_groups_cap;
+    uint32_t* group_cv;         // [n_groups_cap * 8]
+    uint8_t* chunk_hash;        // [n_slots * 32]
+    // K4
+    uint8_t* node_hash[2];      // ping-pong [n_slots * 32]; level 0 aliases chunk_hash
+    uint64_t* node_size[2];     // ping-pong [n_slots]
+    uint32_t* level_count[2];   // [n_files] nodes per file at the current / next level
+    uint32_t* group_start;      // [n_slots] group start indices within a file's level
+    uint8_t* file_root;         // [n_files * 32]
+    uint8_t* file_hash;         // [n_files * 32]
+    // dense outputs
+    uint64_t* out_end;          // [n_slots] file-relative ends, dense by file_chunk_base
+    uint8_t* out_hash;          // [n_slots * 32]
+    // scan scratch
+    uint64_t* scan_partial;     // [scan_blocks_cap]
+    uint64_t* scalars;          // [8] device scalars: 0 = n_cand, 1 = n_groups, 2 = n_chunks
+    uint32_t max_levels;        // host bound on merkle depth
+};
+
+enum { kScalarCand = 0, kScalarGroups = 1, kScalarChunks = 2, kScalarFlags = 3 };
+
+// Launchers (all asynchronous on `st`); each returns the number of kernels it launched.
+int launch_fill_splitmix(uint8_t* dst, uint64_t seed, uint64_t byte_off, uint64_t len, cudaStream_t st);
+int launch_gear(const PipelineBuffers& b, cudaStream_t st);
+// Range mode (one "file" that is a byte range of a larger file): the walk starts at the absolute
+// position walk_start, the buffer end is NOT the end of the file unless is_eof, and the walk stops at
+// the first cut beyond the buffer.  Whole-file mode: walk_start is ignored (range == nullptr).
+struct RangeWalk {
+    uint64_t walk_start;   // absolute position in data of the entry cut
+    uint32_t is_eof;       // buffer end == file end
+};
+int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_t st);
+int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st);
+int launch_merkle(const PipelineBuffers& b, cudaStream_t st);
+int launch_gather(const PipelineBuffers& b, cudaStream_t st);
+int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* partial, uint64_t* total_out,
+                    cudaStream_t st);
+
+inline uint64_t scan_blocks(uint64_t n) { return (n + 2047) / 2048; }
+
+}  // namespace xetgpu

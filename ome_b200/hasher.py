@@ -1,0 +1,259 @@
+"""XetHasher: the host-side handle over libxetgpu's C ABI.
+
+Naming follows the reference's Go binding (pkg/xet/xet.go): a handle created once and closed
+explicitly (NewClient/Close, xet.go:241-308), errors carried as a typed exception with the
+reference's code/message/details triple (XetError, xet.go:227-238, 507-522), progress delivered
+through a handler callback (SetProgressHandler, xet.go:93-151).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Callable, Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+
+MEM_AUTO, MEM_HOST, MEM_DEVICE = 0, 1, 2
+WANT_CHUNKS = 1
+CTX_STAGE_TIMING = 1
+
+MIN_CHUNK, TARGET_CHUNK, MAX_CHUNK = 8192, 65536, 131072
+RANGE_LEAD = MAX_CHUNK + 64
+
+ERR_INVALID_CONFIG, ERR_NOT_FOUND, ERR_CHECKSUM_MISMATCH, ERR_CANCELLED, ERR_IO, ERR_UNKNOWN = 1, 4, 6, 7, 8, 99
+
+
+class XetGpuError(RuntimeError):
+    """Mirror of the Go XetError (pkg/xet/xet.go:227-238): code, message, details."""
+
+    def __init__(self, code: int, message: str, details: str = ""):
+        self.code, self.message, self.details = code, message, details
+        super().__init__(f"xet error {code}: {message}" + (f" ({details})" if details else ""))
+
+
+def _check(errp) -> None:
+    if not errp:
+        return
+    e = errp.contents
+    code = e.code
+    msg = (e.message or b"").decode(errors="replace")
+    det = (e.details or b"").decode(errors="replace")
+    L.load().xetgpu_free_error(errp)
+    raise XetGpuError(code, msg, det)
+
+
+def hash_to_hex(h: bytes) -> str:
+    """MerkleHash::hex — four LE u64 words as %016x (what the Hub prints as X-Xet-Hash)."""
+    assert len(h) == 32
+    out = C.create_string_buffer(65)
+    L.load().xetgpu_hash_to_hex((C.c_uint8 * 32).from_buffer_copy(h), out)
+    return out.value.decode()
+
+
+def hash_from_hex(s: str) -> bytes:
+    out = (C.c_uint8 * 32)()
+    _check(L.load().xetgpu_hash_from_hex(s.encode(), out))
+    return bytes(out)
+
+
+@dataclass
+class FileHash:
+    file_hash: bytes      # raw digest order
+    merkle_root: bytes
+    size: int
+    n_chunks: int
+    first_chunk: int
+
+    @property
+    def hex(self) -> str:
+        return hash_to_hex(self.file_hash)
+
+
+@dataclass
+class ChunkList:
+    files: list                      # [FileHash]
+    chunk_ends: Optional[np.ndarray]    # uint64 [n_chunks], file-relative exclusive ends
+    chunk_hashes: Optional[np.ndarray]  # uint8 [n_chunks, 32]
+
+    def chunks_of(self, f: int):
+        fr = self.files[f]
+        sl = slice(fr.first_chunk, fr.first_chunk + fr.n_chunks)
+        return self.chunk_ends[sl], self.chunk_hashes[sl]
+
+
+@dataclass
+class RangeResult:
+    exit_cut: int
+    chunk_ends: np.ndarray      # file-relative
+    chunk_hashes: np.ndarray
+
+
+def _ptr_of(data):
+    """(address, nbytes, keepalive) of bytes / numpy / torch tensor / raw int address."""
+    if isinstance(data, int):
+        return data, None, None
+    if hasattr(data, "data_ptr"):       # torch tensor (host or device)
+        return data.data_ptr(), data.numel() * data.element_size(), data
+    if isinstance(data, np.ndarray):
+        a = np.ascontiguousarray(data)
+        return a.ctypes.data, a.nbytes, a
+    a = np.frombuffer(data, dtype=np.uint8)
+    return a.ctypes.data, a.nbytes, a
+
+
+class XetHasher:
+    """One context on one GPU.  Thread-compatible like the reference client: calls serialise."""
+
+    def __init__(self, device: int = -1, stream: int = 0, staging_bytes: int = 0, max_batch_bytes: int = 0,
+                 stage_timing: bool = False):
+        self._lib = L.load()
+        cfg = L.XetGpuConfig(device, stream or None, staging_bytes, max_batch_bytes,
+                             CTX_STAGE_TIMING if stage_timing else 0)
+        ctx = L.CTX()
+        _check(self._lib.xetgpu_context_new(C.byref(cfg), C.byref(ctx)))
+        self._ctx = ctx
+        self._cb = None
+
+    # -- lifecycle (Close in pkg/xet/xet.go:288-308)
+    def close(self) -> None:
+        if getattr(self, "_ctx", None):
+            self._lib.xetgpu_context_free(self._ctx)
+            self._ctx = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- progress (SetProgressHandler in pkg/xet/xet.go:93-151)
+    def set_progress_handler(self, handler: Optional[Callable[[dict], None]], throttle_ms: int = 200) -> None:
+        if handler is None:
+            self._cb = None
+            _check(self._lib.xetgpu_context_set_progress_callback(self._ctx, L.ProgressCallback(0), None, 0))
+            return
+
+        def bridge(update, _user):
+            u = update.contents
+            handler(dict(phase=u.phase, total_bytes=u.total_bytes, completed_bytes=u.completed_bytes,
+                         total_files=u.total_files, completed_files=u.completed_files,
+                         current_file=(u.current_file or b"").decode(errors="replace")))
+
+        self._cb = L.ProgressCallback(bridge)
+        _check(self._lib.xetgpu_context_set_progress_callback(self._ctx, self._cb, None, throttle_ms))
+
+    # -- results
+    def _take(self, resp, want_chunks: bool) -> ChunkList:
+        r = resp.contents
+        files = []
+        for i in range(r.n_files):
+            f = r.files[i]
+            files.append(FileHash(bytes(f.file_hash), bytes(f.merkle_root), f.size, f.n_chunks, f.first_chunk))
+        ends = hashes = None
+        if want_chunks:
+            n = r.n_chunks
+            if n:
+                ends = np.ctypeslib.as_array(r.chunk_ends, shape=(n,)).copy()
+                hashes = np.ctypeslib.as_array(r.chunk_hashes, shape=(n * 32,)).reshape(n, 32).copy()
+            else:
+                ends = np.zeros(0, dtype=np.uint64)
+                hashes = np.zeros((0, 32), dtype=np.uint8)
+        self._lib.xetgpu_free_result(resp)
+        return ChunkList(files, ends, hashes)
+
+    # -- hashing
+    def hash_buffers(self, data, offsets: Sequence[int], memory: int = MEM_AUTO, want_chunks: bool = False) -> ChunkList:
+        """Files packed back to back in `data` (bytes, numpy, torch tensor or raw address)."""
+        addr, _, keep = _ptr_of(data)
+        off = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n_files = max(off.size - 1, 0)
+        resp = C.POINTER(L.XetGpuResult)()
+        _check(self._lib.xetgpu_hash_buffers(self._ctx, addr, off.ctypes.data_as(C.POINTER(C.c_uint64)), n_files,
+                                             memory, WANT_CHUNKS if want_chunks else 0, C.byref(resp)))
+        del keep
+        return self._take(resp, want_chunks)
+
+    def hash_bytes(self, data, memory: int = MEM_AUTO, want_chunks: bool = False) -> ChunkList:
+        _, n, _ = _ptr_of(data)
+        return self.hash_buffers(data, [0, n], memory, want_chunks)
+
+    def hash_files(self, paths: Sequence[str], want_chunks: bool = False,
+                   should_cancel: Optional[Callable[[], bool]] = None) -> ChunkList:
+        arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+        tok = None
+        if should_cancel is not None:
+            cb = L.CancellationCallback(lambda _u: bool(should_cancel()))
+            tok = L.XetCancellationToken(cb, None)
+        resp = C.POINTER(L.XetGpuResult)()
+        _check(self._lib.xetgpu_hash_files(self._ctx, arr, len(paths), WANT_CHUNKS if want_chunks else 0,
+                                           C.byref(tok) if tok is not None else None, C.byref(resp)))
+        return self._take(resp, want_chunks)
+
+    def hash_file(self, path: str) -> str:
+        """Xet file hash of one file as the 64-digit hex the Hub advertises."""
+        return self.hash_files([path]).files[0].hex
+
+    # -- verification (shape precedent: hub.VerifyChecksum, pkg/hfutil/hub/utils.go:139-158)
+    def verify_file(self, path: str, expected_hex: str) -> None:
+        _check(self._lib.xetgpu_verify_file(self._ctx, path.encode(), expected_hex.encode()))
+
+    def verify_buffer(self, data, expected_hex: str, memory: int = MEM_AUTO) -> None:
+        addr, n, keep = _ptr_of(data)
+        _check(self._lib.xetgpu_verify_buffer(self._ctx, addr, n, memory, expected_hex.encode()))
+        del keep
+
+    # -- stage-level
+    def gear_candidates(self, data, memory: int = MEM_AUTO) -> np.ndarray:
+        addr, n, keep = _ptr_of(data)
+        out = C.POINTER(C.c_uint64)()
+        cnt = C.c_uint64()
+        _check(self._lib.xetgpu_gear_candidates(self._ctx, addr, n, memory, C.byref(out), C.byref(cnt)))
+        res = np.ctypeslib.as_array(out, shape=(cnt.value,)).copy() if cnt.value else np.zeros(0, dtype=np.uint64)
+        self._lib.xetgpu_free_u64(out)
+        del keep
+        return res
+
+    def hash_range(self, data, file_len: int, range_begin: int, range_end: int, entry_cut: int,
+                   memory: int = MEM_AUTO) -> RangeResult:
+        addr, _, keep = _ptr_of(data)
+        resp = C.POINTER(L.XetGpuResult)()
+        exit_cut = C.c_uint64()
+        _check(self._lib.xetgpu_hash_range(self._ctx, addr, memory, file_len, range_begin, range_end, entry_cut,
+                                           C.byref(exit_cut), C.byref(resp)))
+        del keep
+        cl = self._take(resp, True)
+        return RangeResult(exit_cut.value, cl.chunk_ends, cl.chunk_hashes)
+
+    def range_exit_cut(self, data, file_len: int, range_begin: int, range_end: int, entry_cut: int,
+                       memory: int = MEM_AUTO) -> int:
+        addr, _, keep = _ptr_of(data)
+        exit_cut = C.c_uint64()
+        _check(self._lib.xetgpu_range_exit_cut(self._ctx, addr, memory, file_len, range_begin, range_end, entry_cut,
+                                               C.byref(exit_cut)))
+        del keep
+        return exit_cut.value
+
+    def merkle_from_chunks(self, chunk_hashes: np.ndarray, chunk_sizes: np.ndarray):
+        h = np.ascontiguousarray(chunk_hashes, dtype=np.uint8).reshape(-1)
+        s = np.ascontiguousarray(chunk_sizes, dtype=np.uint64)
+        root = (C.c_uint8 * 32)()
+        fh = (C.c_uint8 * 32)()
+        _check(self._lib.xetgpu_merkle_from_chunks(self._ctx, h.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                   s.ctypes.data_as(C.POINTER(C.c_uint64)), s.size, root, fh))
+        return bytes(root), bytes(fh)
+
+    def fill_splitmix(self, device_ptr: int, seed: int, byte_off: int, length: int) -> None:
+        _check(self._lib.xetgpu_fill_splitmix(self._ctx, device_ptr, seed & (2**64 - 1), byte_off, length))
+
+    def last_timings(self) -> dict:
+        t = L.XetGpuTimings()
+        _check(self._lib.xetgpu_last_timings(self._ctx, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in L.XetGpuTimings._fields_}

@@ -1,0 +1,278 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle and the hf_xet golden vectors.
+
+Bar: bit-exact — every chunk boundary, chunk hash, merkle root and file hash.
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import xet_inputs
+import xet_oracle
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = load_golden()
+SMALL = [c for c in GOLDEN["cases"] if not c.get("large")]
+LARGE = [c for c in GOLDEN["cases"] if c.get("large")]
+
+
+def check_against_oracle(cl, f, data):
+    """File f of ChunkList cl vs the oracle run on `data`."""
+    import ome_b200
+    ref = xet_oracle.hash_file(data)
+    fr = cl.files[f]
+    ends, hashes = cl.chunks_of(f)
+    assert fr.size == data.size
+    assert fr.n_chunks == ref.chunk_ends.size
+    assert np.array_equal(ends, ref.chunk_ends)
+    assert np.array_equal(hashes, ref.chunk_hashes)
+    assert fr.merkle_root == ref.merkle_root
+    assert fr.file_hash == ref.file_hash
+    return ome_b200.hash_to_hex(fr.file_hash)
+
+
+@pytest.mark.parametrize("case", SMALL, ids=[c["name"] for c in SMALL])
+def test_golden_case_host_input(hasher, case):
+    data = xet_inputs.build(case["spec"])
+    cl = hasher.hash_bytes(data, want_chunks=True)
+    fr = cl.files[0]
+    assert fr.hex == case["file_hash"]                      # hf_xet ground truth
+    assert fr.n_chunks == case["n_chunks"]
+    ends, hashes = cl.chunks_of(0)
+    assert [int(x) for x in ends[:16]] == case["cuts_head"]
+    assert hashlib.sha256(ends.astype("<u8").tobytes()).hexdigest() == case["cuts_sha256"]
+    assert hashlib.sha256(hashes.tobytes()).hexdigest() == case["chunk_hashes_sha256"]
+    import ome_b200
+    assert ome_b200.hash_to_hex(fr.merkle_root) == case["merkle_root"]
+    if data.size <= (4 << 20):
+        check_against_oracle(cl, 0, data)
+
+
+@pytest.mark.parametrize("name", ["splitmix_seed1_1MiB", "dense_W_x16384", "deadzone_after_forced",
+                                  "zeros_8x131072", "safetensors_shaped_2MiB", "splitmix_seed2_10MiB"])
+def test_gear_candidates_match_oracle(hasher, name):
+    case = next(c for c in SMALL if c["name"] == name)
+    data = xet_inputs.build(case["spec"])
+    got = hasher.gear_candidates(data)
+    want = xet_oracle.window_candidates(data)
+    # positions < 63 depend on bytes in front of the buffer (there are none): never used by K2
+    assert np.array_equal(got[got >= 63], want[want >= 63])
+
+
+def test_dense_candidates_overflow_path(hasher):
+    """64 MiB of the 64-byte W pattern: 1M candidates, every tile overflows the staged list."""
+    case = next(c for c in SMALL if c["name"] == "dense_W_x1048576")
+    data = xet_inputs.build(case["spec"])
+    got = hasher.gear_candidates(data)
+    want = xet_oracle.window_candidates(data)
+    assert np.array_equal(got[got >= 63], want[want >= 63])
+    assert hasher.hash_bytes(data).files[0].hex == case["file_hash"]
+
+
+def test_all_golden_cases_in_one_batch(hasher):
+    """Many small files packed in one call (BASELINE config 5 shape): per-file state must reset."""
+    cases = [c for c in SMALL if c["n"] <= (2 << 20)]
+    datas = [xet_inputs.build(c["spec"]) for c in cases]
+    offsets = np.concatenate([[0], np.cumsum([d.size for d in datas])]).astype(np.uint64)
+    packed = np.concatenate([d for d in datas if d.size] or [np.zeros(0, np.uint8)])
+    cl = hasher.hash_buffers(packed, offsets, want_chunks=True)
+    assert len(cl.files) == len(cases)
+    for f, (c, d) in enumerate(zip(cases, datas)):
+        assert cl.files[f].hex == c["file_hash"], c["name"]
+        check_against_oracle(cl, f, d)
+
+
+def test_ragged_random_files_batch(hasher):
+    rng = np.random.default_rng(11)
+    sizes = [0, 1, 5, 63, 64, 1024, 4096, 4097, 8191, 8192, 8193, 0, 20000, 70001, 131072, 131073, 300000, 1 << 20]
+    sizes += [int(x) for x in np.exp(rng.uniform(np.log(1), np.log(3e6), 30))]
+    datas = [xet_inputs.splitmix_bytes(500 + i, n) for i, n in enumerate(sizes)]
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+    packed = np.concatenate(datas)
+    cl = hasher.hash_buffers(packed, offsets, want_chunks=True)
+    for f, d in enumerate(datas):
+        check_against_oracle(cl, f, d)
+
+
+def test_nonzero_first_offset_and_unaligned_views(hasher):
+    data = xet_inputs.splitmix_bytes(77, (3 << 20) + 123)
+    for lead in (1, 7, 16, 33):
+        cl = hasher.hash_buffers(data, [lead, data.size], want_chunks=True)
+        check_against_oracle(cl, 0, data[lead:])
+
+
+def test_device_resident_input(hasher):
+    import torch
+    data = xet_inputs.build([["splitmix", 5, (9 << 20) + 17]])
+    t = torch.from_numpy(data).cuda()
+    cl = hasher.hash_buffers(t, [0, data.size], want_chunks=True)
+    check_against_oracle(cl, 0, data)
+    # unaligned device view (base + 3 bytes) takes the device-to-device realignment path
+    cl = hasher.hash_buffers(t[3:], [0, data.size - 3], want_chunks=True)
+    check_against_oracle(cl, 0, data[3:])
+
+
+def test_fill_splitmix_matches_host_generator(hasher):
+    import torch
+    n = (1 << 20) + 13
+    buf = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    for seed, dst_off, stream_off in [(1, 0, 0), (9, 3, 0), (2**64 - 3, 8, 5), (12, 1, 7)]:
+        hasher.fill_splitmix(buf.data_ptr() + dst_off, seed, stream_off, n)
+        torch.cuda.synchronize()
+        got = buf[dst_off:dst_off + n].cpu().numpy()
+        assert np.array_equal(got, xet_inputs.splitmix_bytes(seed, n, stream_off))
+
+
+def test_merkle_from_chunks(hasher):
+    rng = np.random.default_rng(5)
+    for n in [0, 1, 2, 3, 4, 8, 9, 10, 11, 19, 100, 1000, 8192, 50001]:
+        hashes = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        sizes = rng.integers(1, 131073, n).astype(np.uint64)
+        root, fh = hasher.merkle_from_chunks(hashes, sizes)
+        if n:
+            assert root == xet_oracle.merkle_root(hashes, sizes)
+        assert fh == xet_oracle.file_hash_from_chunks(hashes, sizes)
+    # sizes beyond 32 bits (upper merkle levels of > 4 GiB files print > 10 decimal digits)
+    hashes = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+    sizes = rng.integers(1 << 33, 1 << 40, 40).astype(np.uint64)
+    root, fh = hasher.merkle_from_chunks(hashes, sizes)
+    assert root == xet_oracle.merkle_root(hashes, sizes)
+    # uniform fan-out: every hash ends a group / no hash ends a group
+    for byte24 in (0, 1):
+        hashes = np.full((300, 32), byte24, dtype=np.uint8)
+        sizes = np.full(300, 8192, dtype=np.uint64)
+        assert hasher.merkle_from_chunks(hashes, sizes)[0] == xet_oracle.merkle_root(hashes, sizes)
+
+
+@pytest.mark.parametrize("nranges", [2, 3, 5])
+def test_byte_range_partition_reassembles(hasher, nranges):
+    """BASELINE config 4 shape on one GPU: ranges processed in order with the carried cut."""
+    data = xet_inputs.build([["splitmix", 31, 3 << 20], ["zeros", 400000], ["splitmix", 32, (2 << 20) + 999]])
+    n = data.size
+    ref = xet_oracle.hash_file(data)
+    bounds = [n * i // nranges for i in range(nranges + 1)]
+    bounds = [b + (17 if 0 < b < n else 0) for b in bounds]   # unaligned split points
+    entry, ends, hashes = 0, [], []
+    for r in range(nranges):
+        b0, b1 = bounds[r], bounds[r + 1]
+        lead = min(b0, 131072 + 64)
+        piece = data[b0 - lead:b1]
+        spec_exit = hasher.range_exit_cut(piece, n, b0, b1, entry)
+        res = hasher.hash_range(piece, n, b0, b1, entry)
+        assert res.exit_cut == spec_exit
+        assert all(b0 < int(e) <= b1 for e in res.chunk_ends)
+        ends.append(res.chunk_ends)
+        hashes.append(res.chunk_hashes)
+        entry = res.exit_cut
+    ends = np.concatenate(ends)
+    hashes = np.concatenate(hashes)
+    assert np.array_equal(ends, ref.chunk_ends)
+    assert np.array_equal(hashes, ref.chunk_hashes)
+    sizes = np.diff(np.concatenate([[0], ends])).astype(np.uint64)
+    root, fh = hasher.merkle_from_chunks(hashes, sizes)
+    assert root == ref.merkle_root and fh == ref.file_hash
+
+
+def test_hash_files_and_verify(hasher, tmp_path):
+    import ome_b200
+    specs = {"a.safetensors": [["splitmix", 90, (5 << 20) + 3]], "empty.bin": [], "small.json": [["ascii", "{}"]],
+             "zeros.bin": [["zeros", 300000]]}
+    paths, datas = [], []
+    for name, spec in specs.items():
+        d = xet_inputs.build(spec)
+        p = tmp_path / name
+        d.tofile(p)
+        paths.append(str(p))
+        datas.append(d)
+    seen = []
+    hasher.set_progress_handler(lambda u: seen.append(u), throttle_ms=0)
+    cl = hasher.hash_files(paths, want_chunks=True)
+    hasher.set_progress_handler(None)
+    assert seen and seen[-1]["completed_bytes"] == sum(d.size for d in datas)
+    for f, d in enumerate(datas):
+        hexhash = check_against_oracle(cl, f, d)
+        hasher.verify_file(paths[f], hexhash)
+    assert hasher.hash_file(paths[0]) == cl.files[0].hex
+    bad = "0" * 64
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.verify_file(paths[0], bad)
+    assert ei.value.code == 6 and cl.files[0].hex in ei.value.details   # ChecksumMismatch
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.verify_file(str(tmp_path / "missing"), bad)
+    assert ei.value.code == 4                                           # NotFound
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.verify_buffer(datas[0], "xyz")
+    assert ei.value.code == 1                                           # InvalidConfig
+    hasher.verify_buffer(datas[0], cl.files[0].hex)
+    # small batches force several device round trips
+    small = ome_b200.XetHasher(staging_bytes=1 << 20, max_batch_bytes=1 << 20)
+    cl2 = small.hash_files(paths, want_chunks=True)
+    small.close()
+    for f, d in enumerate(datas):
+        check_against_oracle(cl2, f, d)
+    assert hasher.hash_files(paths, should_cancel=lambda: False).files[0].hex == cl.files[0].hex
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.hash_files(paths, should_cancel=lambda: True)
+    assert ei.value.code == 7                                           # Cancelled
+
+
+def test_invalid_arguments(hasher):
+    import ome_b200
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.hash_buffers(np.zeros(10, np.uint8), [5, 2])
+    assert ei.value.code == 1
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.hash_range(np.zeros(100, np.uint8), 100, 50, 40, 0)
+    assert ei.value.code == 1
+
+
+@pytest.mark.parametrize("case", LARGE, ids=[c["name"] for c in LARGE])
+def test_file_larger_than_4GiB(hasher, case):
+    """N > 2^32: u64 offsets everywhere, > 10-digit sizes in upper merkle levels, 36,872 chunks."""
+    import torch
+    n = case["n"]
+    buf = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    spec = case["spec"]
+    assert spec[0][0] == "splitmix" and spec[1][0] == "zeros"
+    hasher.fill_splitmix(buf.data_ptr(), spec[0][1], 0, spec[0][2])
+    cl = hasher.hash_buffers(buf, [0, n], want_chunks=True)
+    assert cl.files[0].hex == case["file_hash"]
+    assert cl.files[0].n_chunks == case["n_chunks"]
+    ends, hashes = cl.chunks_of(0)
+    assert [int(x) for x in ends[:16]] == case["cuts_head"]
+    assert hashlib.sha256(ends.astype("<u8").tobytes()).hexdigest() == case["cuts_sha256"]
+    assert hashlib.sha256(hashes.tobytes()).hexdigest() == case["chunk_hashes_sha256"]
+
+
+def test_full_size_shard_properties(hasher):
+    """1 GiB device-resident shard (BASELINE config 1 size), checked through size-independent
+    properties: (a) the two halves hashed as byte ranges with a carried cut reassemble to the
+    whole-file chunk list; (b) merkle of the returned chunk list reproduces the file hash;
+    (c) chunk sizes respect min/max; (d) a 64 MiB prefix agrees with the oracle."""
+    import torch
+    n = 1 << 30
+    buf = torch.empty(n, dtype=torch.uint8, device="cuda")
+    hasher.fill_splitmix(buf.data_ptr(), 1, 0, n)
+    cl = hasher.hash_buffers(buf, [0, n], want_chunks=True)
+    ends, hashes = cl.chunks_of(0)
+    sizes = np.diff(np.concatenate([[0], ends])).astype(np.uint64)
+    assert int(ends[-1]) == n and sizes.max() <= 131072 and sizes[:-1].min() >= 8192
+    root, fh = hasher.merkle_from_chunks(hashes, sizes)
+    assert root == cl.files[0].merkle_root and fh == cl.files[0].file_hash
+    # (a) two ranges
+    mid = (n // 2) + 12345
+    lead = 131072 + 64
+    r0 = hasher.hash_range(buf, n, 0, mid, 0)
+    r1 = hasher.hash_range(buf[mid - lead:], n, mid, n, r0.exit_cut)
+    assert np.array_equal(np.concatenate([r0.chunk_ends, r1.chunk_ends]), ends)
+    assert np.array_equal(np.concatenate([r0.chunk_hashes, r1.chunk_hashes]), hashes)
+    # (d) prefix parity: first 64 MiB is golden case splitmix_seed1_64MiB
+    case = next(c for c in SMALL if c["name"] == "splitmix_seed1_64MiB")
+    k = case["n_chunks"] - 1      # all but the prefix's last (EOF-flushed) chunk are shared
+    assert [int(x) for x in ends[:16]] == case["cuts_head"]
+    pref = xet_oracle.hash_file(xet_inputs.splitmix_bytes(1, 64 << 20))
+    assert np.array_equal(ends[:k], pref.chunk_ends[:k])
+    assert np.array_equal(hashes[:k], pref.chunk_hashes[:k])
