@@ -135,6 +135,8 @@ typedef struct {
     float merkle_ms;    /* K4: merkle levels + file hash */
     float d2h_ms;
     float total_ms;
+    float gear_kernel_ms;   /* gear_scan_kernel alone (the K1 hot kernel) */
+    float leaf_kernel_ms;   /* leaf_group_kernel alone (the K3 hot kernel, dominant overall) */
     uint64_t bytes;
     uint64_t n_chunks;
     uint64_t n_candidates;

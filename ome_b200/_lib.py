@@ -47,7 +47,8 @@ class XetGpuResult(C.Structure):
 class XetGpuTimings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("gear_ms", C.c_float), ("resolve_ms", C.c_float),
                 ("blake3_ms", C.c_float), ("merkle_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("total_ms", C.c_float), ("bytes", C.c_uint64), ("n_chunks", C.c_uint64),
+                ("total_ms", C.c_float), ("gear_kernel_ms", C.c_float),
+                ("leaf_kernel_ms", C.c_float), ("bytes", C.c_uint64), ("n_chunks", C.c_uint64),
                 ("n_candidates", C.c_uint64), ("kernel_launches", C.c_uint32)]
 
 

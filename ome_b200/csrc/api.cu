@@ -99,6 +99,7 @@ struct XetGpuContext {
     uint64_t cand_cap_hint = 0;
     // timing
     cudaEvent_t ev[8] = {};
+    cudaEvent_t ev_kernel[4] = {};
     XetGpuTimings last = {};
     // progress
     XetProgressCallback progress = nullptr;
@@ -162,6 +163,7 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
         c->own_stream = true;
     }
     for (auto& ev : c->ev) cudaEventCreate(&ev);
+    for (auto& ev : c->ev_kernel) cudaEventCreate(&ev);
     for (auto& ev : c->stage_free) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
     init_gear_kernels();
     init_chunk_hash_kernels();
@@ -184,6 +186,8 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
         if (p) cudaFreeHost(p);
     if (c->h_meta) cudaFreeHost(c->h_meta);
     for (auto& ev : c->ev)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->ev_kernel)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : c->stage_free)
         if (ev) cudaEventDestroy(ev);
@@ -420,6 +424,8 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
         PipelineBuffers b{};
         if (XetError* e = ensure_workspace(c, plan, &b)) return e;
         b.data = d_data;
+        if (timing)
+            for (int i = 0; i < 4; i++) b.ev_kernel[i] = c->ev_kernel[i];
         // metadata upload through pinned memory
         const uint64_t F = n_files;
         const uint64_t meta_bytes = (F + 1) * 16 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
@@ -531,6 +537,10 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
             cudaEventElapsedTime(&t.merkle_ms, c->ev[3], c->ev[4]);
             cudaEventElapsedTime(&t.d2h_ms, c->ev[4], c->ev[6]);
             cudaEventElapsedTime(&t.total_ms, c->ev[0], c->ev[6]);
+            t.gear_kernel_ms = t.leaf_kernel_ms = 0.f;
+            if (plan.n_tiles) cudaEventElapsedTime(&t.gear_kernel_ms, c->ev_kernel[0], c->ev_kernel[1]);
+            if (!opt.resolve_only && plan.n_slots && plan.n_groups_cap)
+                cudaEventElapsedTime(&t.leaf_kernel_ms, c->ev_kernel[2], c->ev_kernel[3]);
         }
         c->last.bytes = total;
         c->last.n_chunks = n_chunks;

@@ -200,8 +200,10 @@ int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st) {
     if (b.n_slots == 0 || b.n_groups_cap == 0) return n;
     const uint64_t warps = (b.n_groups_cap + 31) / 32;
     const unsigned blocks = (unsigned)((warps + kLeafWarpsPerCta - 1) / kLeafWarpsPerCta);
+    if (b.ev_kernel[2]) cudaEventRecord(b.ev_kernel[2], st);
     leaf_group_kernel<<<blocks, kLeafThreads, kLeafSmem, st>>>(b.data, b.scalars, b.group_chunk, b.group_off,
                                                                b.chunk_start, b.chunk_len, b.group_cv, b.chunk_hash);
+    if (b.ev_kernel[3]) cudaEventRecord(b.ev_kernel[3], st);
     chunk_tree_kernel<<<(unsigned)((b.n_slots + 127) / 128), 128, 0, st>>>(b.n_slots, b.slot_groups, b.group_off,
                                                                           b.group_cv, b.chunk_hash);
     return n + 2;

@@ -313,7 +313,9 @@ int launch_gear(const PipelineBuffers& b, cudaStream_t st) {
         cudaMemsetAsync(b.scalars + kScalarCand, 0, sizeof(uint64_t), st);
         return 0;
     }
+    if (b.ev_kernel[0]) cudaEventRecord(b.ev_kernel[0], st);
     gear_scan_kernel<<<b.n_tiles, kGearThreads, kGearSmem, st>>>(b.data, b.total_bytes, b.tile_count, b.tile_stage);
+    if (b.ev_kernel[1]) cudaEventRecord(b.ev_kernel[1], st);
     int n = 1 + launch_scan_u32(b.tile_count, b.tile_off, b.n_tiles, b.scan_partial, b.scalars + kScalarCand, st);
     gear_compact_kernel<<<b.n_tiles, kGearThreads, kGearSmem, st>>>(b.data, b.total_bytes, b.tile_count, b.tile_stage,
                                                                     b.tile_off, b.cand, b.cand_cap);

@@ -71,6 +71,8 @@ struct PipelineBuffers {
     uint64_t* scan_partial;     // [scan_blocks_cap]
     uint64_t* scalars;          // [8] device scalars: 0 = n_cand, 1 = n_groups, 2 = n_chunks
     uint32_t max_levels;        // host bound on merkle depth
+    // optional timing events (nullptr = off): [0,1] around gear_scan_kernel, [2,3] around leaf_group_kernel
+    cudaEvent_t ev_kernel[4];
 };
 
 enum { kScalarCand = 0, kScalarGroups = 1, kScalarChunks = 2, kScalarFlags = 3 };
