@@ -232,6 +232,27 @@ XetError* xetgpu_merkle_from_chunks(XetGpuContext* ctx, const uint8_t* chunk_has
                                     const uint64_t* chunk_sizes, uint64_t n_chunks,
                                     uint8_t out_merkle_root[32], uint8_t out_file_hash[32]);
 
+/*
+ * Same result as xetgpu_merkle_from_chunks, for callers that cannot allocate device memory.
+ * No counterpart in the reference: OME has no GPU code, so it never meets this constraint.
+ * A process whose GPU memory is wholly owned by another allocator, a latency path that cannot
+ * take the implicit synchronisation of cudaMalloc/cudaFree, or a combiner that holds no
+ * XetGpuContext can call this instead: it needs no context and allocates nothing.  Its scratch
+ * is a fixed array inside the library image (about 2.2 MB per GPU that loads the library, held
+ * until exit), which caps the list at XETGPU_STATIC_MERKLE_MAX_CHUNKS entries; longer lists get
+ * error code 1.  Inputs and outputs are DEVICE pointers owned by the caller (hashes: 32 bytes
+ * per chunk, raw digest order; sizes: u64; outputs: 32 bytes each).  One kernel is launched on
+ * `stream` (a cudaStream_t, NULL = default stream) and the call returns without waiting.
+ * The first call on each device also looks up the array's device address — make that call
+ * before starting any stream capture.  All calls share the array: calls that can overlap on
+ * the GPU must be serialised by the caller.
+ */
+#define XETGPU_STATIC_MERKLE_MAX_CHUNKS 65536u
+XetError* xetgpu_merkle_from_chunks_static(const uint8_t* device_chunk_hashes,
+                                           const uint64_t* device_chunk_sizes, uint64_t n_chunks,
+                                           uint8_t* device_out_merkle_root, uint8_t* device_out_file_hash,
+                                           void* stream);
+
 /* K0: fill device memory with the SURVEY.md §8(d) counter-based splitmix64 stream:
  * dst[i] = byte (byte_off + i) of stream `seed`.  Benchmarks and tests only. */
 XetError* xetgpu_fill_splitmix(XetGpuContext* ctx, void* device_dst, uint64_t seed, uint64_t byte_off,

@@ -77,6 +77,8 @@ SIGNATURES = {
                                      C.POINTER(C.c_uint64)]),
     "xetgpu_merkle_from_chunks": (ERRP, [CTX, C.POINTER(C.c_uint8), C.POINTER(C.c_uint64), C.c_uint64,
                                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]),
+    "xetgpu_merkle_from_chunks_static": (ERRP, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                                C.c_void_p]),
     "xetgpu_fill_splitmix": (ERRP, [CTX, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
     "xetgpu_last_timings": (ERRP, [CTX, C.POINTER(XetGpuTimings)]),
     "xetgpu_free_error": (None, [ERRP]),

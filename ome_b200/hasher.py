@@ -103,6 +103,23 @@ def _ptr_of(data):
     return a.ctypes.data, a.nbytes, a
 
 
+STATIC_MERKLE_MAX_CHUNKS = 65536
+
+
+def merkle_from_chunks_static(hashes_dev_ptr: int, sizes_dev_ptr: int, n_chunks: int, out_root_dev_ptr: int,
+                              out_file_hash_dev_ptr: int, stream: int = 0) -> None:
+    """Merkle root + file hash of a device-resident chunk list without any device allocation.
+
+    For callers that may not allocate on the GPU (memory owned by another allocator, latency
+    paths, no XetGpuContext at hand).  All five pointers are device addresses the caller owns;
+    at most STATIC_MERKLE_MAX_CHUNKS chunks; the kernel is only enqueued on `stream` — synchronise
+    before reading the outputs, and do not let two calls overlap on the GPU (they share one
+    fixed scratch array inside the library).
+    """
+    _check(L.load().xetgpu_merkle_from_chunks_static(hashes_dev_ptr, sizes_dev_ptr, n_chunks, out_root_dev_ptr,
+                                                     out_file_hash_dev_ptr, stream or None))
+
+
 class XetHasher:
     """One context on one GPU.  Thread-compatible like the reference client: calls serialise."""
 
