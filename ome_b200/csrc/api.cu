@@ -257,6 +257,8 @@ struct Plan {
     uint64_t cand_cap = 0;
     uint32_t max_levels = 0;
     std::vector<uint64_t> slot_off;  // host prefix
+    std::vector<uint64_t> seg_off;   // host prefix of per-file segment counts (K2)
+    uint64_t n_segs = 0;
 };
 
 static uint32_t bit_length(uint64_t v) {
@@ -273,20 +275,27 @@ static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, u
     p.total = total;
     p.n_files = (uint32_t)n_files;
     p.slot_off.resize(n_files + 1);
-    uint64_t s = 0, max_slots = 0;
+    p.seg_off.resize(n_files + 1);
+    uint64_t s = 0, max_slots = 0, g = 0;
     for (size_t f = 0; f < n_files; f++) {
         p.slot_off[f] = s;
+        p.seg_off[f] = g;
         uint64_t len = offsets[f + 1] - offsets[f];
+        g += (len + kSegBytes - 1) / kSegBytes;
         uint64_t ub = len / kMinChunk + 2;  // every chunk but the last is >= 8192 bytes (+1 sentinel slot)
         max_slots = std::max(max_slots, ub);
         s += ub;
     }
     p.slot_off[n_files] = s;
     p.n_slots = s;
+    p.seg_off[n_files] = g;
+    p.n_segs = g;
     p.n_tiles = (uint32_t)((total + kGearTile - 1) / kGearTile);
     p.n_groups_cap = total / (kLeavesPerGroup * 1024ull) + s;
     p.cand_cap = std::max<uint64_t>(std::max<uint64_t>(total / 1024 + 4096, cand_cap_hint), 1);
-    p.max_levels = bit_length(max_slots) + 1;
+    // every group but the last has >= 3 children, so a level of m nodes yields <= (m + 2) / 3 nodes
+    p.max_levels = 1;
+    for (uint64_t m = max_slots; m > 1; m = (m + 2) / 3) p.max_levels++;
     return p;
 }
 
@@ -309,6 +318,18 @@ static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool
     b->tile_off = a.take<uint64_t>(T + 2);
     b->cand = a.take<uint64_t>(p.cand_cap);
     b->slot_end = a.take<uint64_t>(S + 1);
+    const uint64_t G = p.n_segs;
+    b->n_segs = G;
+    b->seg_off = a.take<uint64_t>(F + 1);
+    b->seg_spec = a.take<uint64_t>(G * kSegCap + 1);
+    b->seg_pre = a.take<uint64_t>(G * kSegCap + 1);
+    b->seg_spec_n = a.take<uint32_t>(G + 1);
+    b->seg_pre_n = a.take<uint32_t>(G + 1);
+    b->seg_merge_idx = a.take<uint32_t>(G + 1);
+    b->seg_final_n = a.take<uint32_t>(G + 1);
+    b->seg_exit_spec = a.take<uint64_t>(G + 1);
+    b->seg_exit_true = a.take<uint64_t>(G + 1);
+    b->seg_base = a.take<uint64_t>(G + 2);
     b->file_count = a.take<uint32_t>(F + 1);
     b->first_start = a.take<uint64_t>(F + 1);
     b->file_chunk_base = a.take<uint64_t>(F + 2);
@@ -327,11 +348,16 @@ static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool
     b->level_count[0] = a.take<uint32_t>(F + 1);
     b->level_count[1] = a.take<uint32_t>(F + 1);
     b->group_start = a.take<uint32_t>(S + 2);
+    b->mk_bits = a.take<uint64_t>(S + 1);
+    b->mk_out = a.take<uint64_t>(S + 1);
+    b->mk_cnt = a.take<uint64_t>(S + 1);
+    b->mk_entry = a.take<uint32_t>(S + 1);
+    b->mk_base = a.take<uint32_t>(S + 1);
     b->file_root = a.take<uint8_t>((F + 1) * 32);
     b->file_hash = a.take<uint8_t>((F + 1) * 32);
     b->out_end = a.take<uint64_t>(S + 1);
     b->out_hash = a.take<uint8_t>((S + 1) * 32);
-    b->scan_partial = a.take<uint64_t>(scan_blocks(std::max<uint64_t>(std::max<uint64_t>(T, S), F) + 2) + 1);
+    b->scan_partial = a.take<uint64_t>(scan_blocks(std::max<uint64_t>(std::max<uint64_t>(std::max<uint64_t>(T, S), F), G) + 2) + 1);
     b->scalars = a.take<uint64_t>(8);
     *need = a.used;
     return nullptr;
@@ -428,17 +454,20 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
             for (int i = 0; i < 4; i++) b.ev_kernel[i] = c->ev_kernel[i];
         // metadata upload through pinned memory
         const uint64_t F = n_files;
-        const uint64_t meta_bytes = (F + 1) * 16 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
+        const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
         if (XetError* e = ensure_meta(c, meta_bytes)) return e;
         uint64_t* h_off = reinterpret_cast<uint64_t*>(c->h_meta);
         uint64_t* h_slot = h_off + (F + 1);
         memcpy(h_off, offsets, (F + 1) * 8);
         memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
+        uint64_t* h_seg = h_slot + (F + 1);
+        memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
         cudaStream_t st = c->stream;
         int launches = 0;
         if (timing) cudaEventRecord(c->ev[0], st);
         CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
         CU(cudaMemsetAsync(b.scalars, 0, 64, st));
         launches += launch_gear(b, st);
         if (timing) cudaEventRecord(c->ev[1], st);
@@ -460,7 +489,7 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
         }
         CU(cudaGetLastError());
         // readback: scalars, per-file counts, bases, roots, hashes
-        uint8_t* h_rb = c->h_meta + (F + 1) * 16;
+        uint8_t* h_rb = c->h_meta + (F + 1) * 24;
         uint64_t* h_scalars = reinterpret_cast<uint64_t*>(h_rb);
         uint64_t* h_base = h_scalars + 8;
         uint32_t* h_count = reinterpret_cast<uint32_t*>(h_base + (F + 2));
@@ -889,7 +918,8 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
     plan.n_tiles = 0;
     plan.n_groups_cap = 1;
     plan.cand_cap = 1;
-    plan.max_levels = bit_length(n_chunks + 1) + 1;
+    plan.max_levels = 1;
+    for (uint64_t m = n_chunks + 1; m > 1; m = (m + 2) / 3) plan.max_levels++;
     PipelineBuffers b{};
     if (XetError* e = ensure_workspace(c, plan, &b)) return e;
     cudaStream_t st = c->stream;

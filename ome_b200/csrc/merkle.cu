@@ -9,19 +9,82 @@
 //   - levels repeat until one node remains; file hash = BLAKE3_keyed(0^32, root)
 // A node message is <= 9 * 89 = 801 bytes, i.e. always a single BLAKE3 leaf (<= 13 blocks).
 //
-// Every file in the batch advances one level per launch pair: a one-thread-per-file greedy scan
-// of the "ends a group" flags, then one thread per new node that formats and hashes its lines.
-// This stage touches 40 bytes per ~64 KiB chunk, so it is launch-bound, not bandwidth-bound.
+// Every file in the batch advances one level per round of launches: the grouping kernels below,
+// then one thread per new node that formats and hashes its lines.  This stage touches 40 bytes
+// per ~64 KiB chunk, so it is launch/latency-bound, not bandwidth-bound.
 #include "blake3_dev.cuh"
 #include "xetgpu_internal.h"
 
 namespace xetgpu {
 
+// ---- grouping -----------------------------------------------------------------------------
+// Cutting a level into groups is a greedy chain (next start = start + k(start), k in 1..9), but the
+// jump is bounded, so the chain through a block of 32 nodes is a function of just the offset
+// (0..8) at which it enters the block.  Per level:
+//   A  one thread per 32-node block tabulates, for each of the 9 possible entry offsets, the exit
+//      offset and the number of group starts inside the block                    (parallel)
+//   B  one thread per file composes the block tables left to right: a shift and a mask per block
+//   C  one thread per block replays its 32 nodes from its now-known entry offset and writes the
+//      group starts                                                             (parallel)
 // Level bookkeeping for file f lives in the file's slot range [slot_off[f], slot_off[f+1]).
-__global__ void merkle_group_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files,
-                                    const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
-                                    uint32_t* __restrict__ next_count, uint32_t* __restrict__ group_start,
-                                    uint8_t* __restrict__ file_root) {
+
+// Children taken by a group starting at block-relative node r, with `rest` nodes left in the
+// level; bits holds the "hash % 4 == 0" flags of block nodes 0..39 (8 nodes of lookahead).
+__device__ __forceinline__ uint32_t group_len(uint64_t bits, uint32_t r, uint32_t rest) {
+    if (rest <= 2) return rest;
+    const uint32_t end = rest < 9 ? rest : 9;
+    const uint32_t m = (uint32_t)(bits >> (r + 2)) & ((1u << (end - 2)) - 1u);  // children 2 .. end-1
+    return m ? (uint32_t)__ffs(m) + 2u : end;
+}
+
+__device__ __forceinline__ uint32_t file_of_slot_g(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t s) {
+    uint32_t lo = 0, hi = n_files;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (slot_off[mid] <= s) lo = mid;
+        else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void merkle_block_map_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
+                                        const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
+                                        uint64_t* __restrict__ block_bits, uint64_t* __restrict__ map_out,
+                                        uint64_t* __restrict__ map_cnt) {
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    const uint32_t f = file_of_slot_g(slot_off, n_files, s);
+    const uint64_t base = slot_off[f];
+    const uint32_t n = cur_count[f];
+    const uint64_t b = s - base;
+    if (n <= 1 || b * 32 >= n) return;
+    const uint32_t first = (uint32_t)b * 32;
+    uint64_t bits = 0;
+    for (uint32_t i = 0; i < 40 && first + i < n; i++)
+        // MerkleHash % 4 == word 3 (LE u64 at bytes 24..31) % 4 == low two bits of byte 24
+        bits |= (uint64_t)((cur_hash[(base + first + i) * 32 + 24] & 3u) == 0u) << i;
+    uint64_t mo = 0, mc = 0;
+    for (uint32_t o = 0; o < 9; o++) {
+        uint32_t r = o, cnt = 0;
+        while (r < 32 && first + r < n) {
+            r += group_len(bits, r, n - (first + r));
+            cnt++;
+        }
+        const uint32_t out = r >= 32 ? r - 32 : 0;
+        mo |= (uint64_t)out << (4 * o);
+        mc |= (uint64_t)cnt << (5 * o);
+    }
+    block_bits[s] = bits;
+    map_out[s] = mo;
+    map_cnt[s] = mc;
+}
+
+__global__ void merkle_compose_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files,
+                                      const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
+                                      const uint64_t* __restrict__ map_out, const uint64_t* __restrict__ map_cnt,
+                                      uint32_t* __restrict__ block_entry, uint32_t* __restrict__ block_base,
+                                      uint32_t* __restrict__ next_count, uint32_t* __restrict__ group_start,
+                                      uint8_t* __restrict__ file_root) {
     const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= n_files) return;
     const uint32_t n = cur_count[f];
@@ -36,29 +99,39 @@ __global__ void merkle_group_kernel(const uint64_t* __restrict__ slot_off, uint3
         next_count[f] = 0;
         return;
     }
-    uint32_t r = 0, ng = 0;
-    while (r < n) {
-        const uint32_t rest = n - r;
-        uint32_t k;
-        if (rest <= 2) {
-            k = rest;
-        } else {
-            const uint32_t end = rest < 9 ? rest : 9;
-            k = end;
-            for (uint32_t i = 2; i < end; i++) {
-                // MerkleHash % 4 == word 3 (LE u64 at bytes 24..31) % 4 == low two bits of byte 24
-                if ((cur_hash[(base + r + i) * 32 + 24] & 3u) == 0u) {
-                    k = i + 1;
-                    break;
-                }
-            }
-        }
-        group_start[base + ng] = r;
-        ng++;
-        r += k;
+    const uint32_t nb = (n + 31) / 32;
+    uint32_t o = 0, total = 0;
+#pragma unroll 8
+    for (uint32_t b = 0; b < nb; b++) {
+        const uint64_t mo = map_out[base + b], mc = map_cnt[base + b];
+        block_entry[base + b] = o;
+        block_base[base + b] = total;
+        total += (uint32_t)(mc >> (5 * o)) & 31u;
+        o = (uint32_t)(mo >> (4 * o)) & 15u;
     }
-    group_start[base + ng] = n;  // sentinel; ng <= n - 1 for n >= 2, so this stays inside the range
-    next_count[f] = ng;
+    group_start[base + total] = n;  // sentinel; total <= (n + 2) / 3 < n for n >= 2
+    next_count[f] = total;
+}
+
+__global__ void merkle_emit_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
+                                   const uint32_t* __restrict__ cur_count, const uint64_t* __restrict__ block_bits,
+                                   const uint32_t* __restrict__ block_entry, const uint32_t* __restrict__ block_base,
+                                   uint32_t* __restrict__ group_start) {
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    const uint32_t f = file_of_slot_g(slot_off, n_files, s);
+    const uint64_t base = slot_off[f];
+    const uint32_t n = cur_count[f];
+    const uint64_t b = s - base;
+    if (n <= 1 || b * 32 >= n) return;
+    const uint32_t first = (uint32_t)b * 32;
+    const uint64_t bits = block_bits[s];
+    uint32_t r = block_entry[s];
+    uint64_t w = base + block_base[s];
+    while (r < 32 && first + r < n) {
+        group_start[w++] = first + r;
+        r += group_len(bits, r, n - (first + r));
+    }
 }
 
 __device__ __forceinline__ uint32_t file_of_slot_m(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t s) {
@@ -187,14 +260,22 @@ int launch_merkle(const PipelineBuffers& b, cudaStream_t st) {
     cudaMemcpyAsync(b.level_count[0], b.file_count, sizeof(uint32_t) * b.n_files, cudaMemcpyDeviceToDevice, st);
     int cur = 0;
     for (uint32_t level = 0; level <= b.max_levels; level++) {
-        merkle_group_kernel<<<fblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
-                                                     b.level_count[cur ^ 1], b.group_start, b.file_root);
+        if (b.n_slots) {
+            merkle_block_map_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
+                                                             b.level_count[cur], b.mk_bits, b.mk_out, b.mk_cnt);
+            n++;
+        }
+        merkle_compose_kernel<<<fblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
+                                                       b.mk_out, b.mk_cnt, b.mk_entry, b.mk_base,
+                                                       b.level_count[cur ^ 1], b.group_start, b.file_root);
         n++;
         if (level == b.max_levels || b.n_slots == 0) break;
+        merkle_emit_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.level_count[cur], b.mk_bits,
+                                                    b.mk_entry, b.mk_base, b.group_start);
         merkle_hash_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
                                                     b.node_size[cur], b.level_count[cur ^ 1], b.group_start,
                                                     b.node_hash[cur ^ 1], b.node_size[cur ^ 1]);
-        n++;
+        n += 2;
         cur ^= 1;
     }
     file_hash_kernel<<<fblocks, 128, 0, st>>>(b.n_files, b.file_count, b.file_root, b.file_hash);

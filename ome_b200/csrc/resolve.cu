@@ -36,17 +36,13 @@ struct CandIndex {
     }
 };
 
-// Walks one file (or one byte range of a file) and writes absolute cut positions.
-//   begin/end    : absolute extent of the bytes present in `data`
-//   walk_start   : absolute position of the cut the walk starts from (== begin for whole files)
-//   is_eof       : `end` is the end of the file (flush the tail); otherwise the walk stops at the
-//                  first cut that would lie beyond `end` (it belongs to the next range)
-__device__ __forceinline__ uint32_t walk_cuts(const CandIndex& ci, uint64_t walk_start, uint64_t end, bool is_eof,
-                                              uint64_t* __restrict__ out, uint64_t out_cap) {
-    uint64_t start = walk_start;
+// Greedy walk from the cut `start`.  on_cut(cut) is called for every cut in order and returns
+// false to stop.  `end` is the end of the bytes present; is_eof says whether that is the end of
+// the file (flush the tail) — otherwise the walk stops at the first cut it cannot decide.
+template <typename F>
+__device__ __forceinline__ void walk_cuts(const CandIndex& ci, uint64_t start, uint64_t end, bool is_eof, F on_cut) {
     uint64_t idx = 0;
     bool have_idx = false;
-    uint32_t n = 0;
     while (true) {
         if (is_eof && start >= end) break;
         uint64_t hi = start + kMaxChunk;
@@ -64,42 +60,237 @@ __device__ __forceinline__ uint32_t walk_cuts(const CandIndex& ci, uint64_t walk
                 if (c + 1 <= hi) cut = c + 1;
             }
         }
-        if (!is_eof && cut > end) break;
-        if (n < out_cap) out[n] = cut;
-        n++;
+        if (!is_eof && cut > end) break;  // belongs to the next byte range
+        if (!on_cut(cut)) break;
         start = cut;
     }
-    return n;
 }
 
-__global__ void resolve_files_kernel(const uint64_t* __restrict__ cand, const uint64_t* __restrict__ tile_off,
-                                     const uint64_t* __restrict__ scalars, uint64_t cand_cap, uint32_t n_tiles,
-                                     const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ slot_off,
-                                     uint32_t n_files, uint64_t* __restrict__ slot_end,
-                                     uint32_t* __restrict__ file_count, uint64_t* __restrict__ first_start,
-                                     RangeWalk range, bool range_mode) {
+// ---- segment-speculative resolution --------------------------------------------------------
+// The greedy walk is a sequential chain (next cut = f(previous cut)), ~N/66 KB steps per file.
+// It is parallelised by speculation: a file is split into kSegBytes segments and
+//   A  every segment walks from its own begin as if a cut were there          (parallel)
+//   A2 every segment j >= 1 re-walks from segment j-1's speculative exit cut until it lands on
+//      a cut of its own speculative chain — from a shared cut on, two chains are identical —
+//      and records the few cuts before that merge point                        (parallel)
+//   B  one warp per file checks, 32 segments at a time, that each segment's assumed entry was
+//      the true exit of its predecessor, and re-walks the rare segment where it was not
+//   C  an exclusive scan of the per-segment final counts and a copy into the file's slots.
+// The result is the sequential chain exactly, for any input: B falls back to walking (worst case:
+// chains that never merge, e.g. long runs without any candidate after an unaligned prefix).
+struct SegArrays {
+    const uint64_t* seg_off;   // [n_files+1] first segment of each file
+    uint64_t* spec;            // [n_segs * kSegCap] speculative cuts
+    uint64_t* pre;             // [n_segs * kSegCap] cuts before the merge point
+    uint32_t* spec_n;          // [n_segs]
+    uint32_t* pre_n;           // [n_segs]
+    uint32_t* merge_idx;       // [n_segs] first speculative cut that is kept
+    uint64_t* exit_spec;       // [n_segs] last cut <= segment end of the speculative chain
+    uint64_t* exit_true;       // [n_segs] same for the re-synchronised chain
+    uint32_t* final_n;         // [n_segs]
+    uint64_t* seg_base;        // [n_segs+1] exclusive scan of final_n
+};
+
+struct FileView {
+    uint64_t begin, end, walk_start;
+    bool is_eof;
+    uint32_t f;
+    uint64_t seg0, seg1;  // this file's segments
+};
+
+__device__ __forceinline__ FileView file_view(uint32_t f, const uint64_t* file_off, const uint64_t* seg_off,
+                                              RangeWalk range, bool range_mode) {
+    FileView v;
+    v.f = f;
+    v.begin = file_off[f];
+    v.end = file_off[f + 1];
+    v.walk_start = range_mode ? range.walk_start : v.begin;
+    v.is_eof = range_mode ? (range.is_eof != 0) : true;
+    v.seg0 = seg_off[f];
+    v.seg1 = seg_off[f + 1];
+    return v;
+}
+
+__device__ __forceinline__ uint32_t file_of_seg(const uint64_t* __restrict__ seg_off, uint32_t n_files, uint64_t s) {
+    uint32_t lo = 0, hi = n_files;  // last f with seg_off[f] <= s (files without segments are skipped)
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (seg_off[mid] <= s) lo = mid;
+        else hi = mid;
+    }
+    return lo;
+}
+
+// Re-synchronise segment s of file v: walk from `entry` until a cut of the speculative chain is hit.
+__device__ __forceinline__ void sync_segment(const CandIndex& ci, const SegArrays& sa, const FileView& v, uint64_t s,
+                                             uint64_t entry) {
+    const uint64_t j = s - v.seg0;
+    const uint64_t seg_e = min(v.end, v.begin + (j + 1) * kSegBytes);
+    const uint64_t* spec = sa.spec + s * kSegCap;
+    uint64_t* pre = sa.pre + s * kSegCap;
+    const uint32_t ns = sa.spec_n[s];
+    uint32_t i = 0, np = 0;
+    bool merged = false;
+    uint64_t last = entry;
+    walk_cuts(ci, entry, v.end, v.is_eof, [&](uint64_t cut) {
+        if (cut > seg_e) return false;
+        while (i < ns && spec[i] < cut) i++;
+        if (i < ns && spec[i] == cut) {
+            merged = true;
+            return false;
+        }
+        if (np < kSegCap) pre[np] = cut;
+        np++;
+        last = cut;
+        return true;
+    });
+    sa.pre_n[s] = np;
+    sa.merge_idx[s] = merged ? i : ns;
+    sa.exit_true[s] = merged ? sa.exit_spec[s] : last;
+    sa.final_n[s] = np + (merged ? ns - i : 0u);
+}
+
+struct ResolveArgs {
+    const uint64_t* cand;
+    const uint64_t* tile_off;
+    const uint64_t* scalars;
+    uint64_t cand_cap;
+    uint32_t n_tiles;
+    const uint64_t* file_off;
+    uint32_t n_files;
+    uint64_t n_segs;
+    RangeWalk range;
+    bool range_mode;
+    SegArrays sa;
+};
+
+__device__ __forceinline__ CandIndex cand_index(const ResolveArgs& a) {
+    uint64_t n_cand = a.scalars[kScalarCand];
+    if (n_cand > a.cand_cap) n_cand = a.cand_cap;  // host detects the overflow and re-runs with a larger list
+    return CandIndex{a.cand, a.tile_off, n_cand, a.n_tiles};
+}
+
+// A: speculative chain of every segment.
+__global__ void resolve_spec_kernel(ResolveArgs a) {
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= a.n_segs) return;
+    const CandIndex ci = cand_index(a);
+    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    const uint64_t j = s - v.seg0;
+    const uint64_t seg_b = v.begin + j * kSegBytes;
+    const uint64_t seg_e = min(v.end, seg_b + kSegBytes);
+    const uint64_t start = j == 0 ? v.walk_start : seg_b;
+    uint64_t* spec = a.sa.spec + s * kSegCap;
+    uint32_t n = 0;
+    uint64_t last = start;
+    walk_cuts(ci, start, v.end, v.is_eof, [&](uint64_t cut) {
+        if (cut > seg_e) return false;
+        if (n < kSegCap) spec[n] = cut;
+        n++;
+        last = cut;
+        return true;
+    });
+    a.sa.spec_n[s] = n;
+    a.sa.exit_spec[s] = last;
+    if (j == 0) {  // the first segment's entry is the true one
+        a.sa.pre_n[s] = 0;
+        a.sa.merge_idx[s] = 0;
+        a.sa.exit_true[s] = last;
+        a.sa.final_n[s] = n;
+    }
+}
+
+// A2: re-synchronise every later segment from its predecessor's speculative exit.
+__global__ void resolve_sync_kernel(ResolveArgs a) {
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= a.n_segs) return;
+    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    if (s == v.seg0) return;
+    sync_segment(cand_index(a), a.sa, v, s, a.sa.exit_spec[s - 1]);
+}
+
+// B: validate the speculation chain, 32 segments per step; repair where the assumed entry was wrong.
+__global__ void resolve_fix_kernel(ResolveArgs a) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (f >= a.n_files) return;
+    const FileView v = file_view(f, a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    const CandIndex ci = cand_index(a);
+    uint64_t s = v.seg0 + 1;
+    while (s < v.seg1) {
+        const uint64_t mine = s + lane;
+        // segment `mine` assumed entry exit_spec[mine-1]; it was right iff that is the predecessor's true exit
+        const bool bad = mine < v.seg1 && a.sa.exit_true[mine - 1] != a.sa.exit_spec[mine - 1];
+        const uint32_t bad_mask = __ballot_sync(0xffffffffu, bad);
+        if (bad_mask == 0) {
+            s += 32;
+            continue;
+        }
+        const uint64_t sb = s + (__ffs(bad_mask) - 1);  // everything before sb is final
+        if (lane == 0) sync_segment(ci, a.sa, v, sb, a.sa.exit_true[sb - 1]);
+        __threadfence_block();
+        __syncwarp();
+        s = sb + 1;
+    }
+}
+
+// C: copy the final cuts of each segment into its file's slot range (one warp per segment).
+__global__ void resolve_stitch_kernel(ResolveArgs a, const uint64_t* __restrict__ slot_off,
+                                      uint64_t* __restrict__ slot_end) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t s = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (s >= a.n_segs) return;
+    const uint32_t f = file_of_seg(a.sa.seg_off, a.n_files, s);
+    const uint64_t s0 = a.sa.seg_off[f];
+    uint64_t* dst = slot_end + slot_off[f] + (a.sa.seg_base[s] - a.sa.seg_base[s0]);
+    const uint64_t room = slot_off[f + 1] - slot_off[f] - (a.sa.seg_base[s] - a.sa.seg_base[s0]);
+    const uint32_t np = a.sa.pre_n[s], mi = a.sa.merge_idx[s], ns = a.sa.spec_n[s];
+    const uint64_t* pre = a.sa.pre + s * kSegCap;
+    const uint64_t* spec = a.sa.spec + s * kSegCap;
+    for (uint32_t i = lane; i < np; i += 32)
+        if (i < room) dst[i] = pre[i];
+    for (uint32_t i = lane; mi + i < ns; i += 32)
+        if (np + i < room) dst[np + i] = spec[mi + i];
+}
+
+__global__ void resolve_file_counts_kernel(ResolveArgs a, uint32_t* __restrict__ file_count,
+                                           uint64_t* __restrict__ first_start) {
     const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= n_files) return;
-    uint64_t n_cand = scalars[kScalarCand];
-    if (n_cand > cand_cap) n_cand = cand_cap;  // host detects the overflow and re-runs with a larger list
-    CandIndex ci{cand, tile_off, n_cand, n_tiles};
-    const uint64_t begin = file_off[f], end = file_off[f + 1];
-    const uint64_t ws = range_mode ? range.walk_start : begin;
-    const bool eof = range_mode ? (range.is_eof != 0) : true;
-    const uint64_t s0 = slot_off[f];
-    file_count[f] = walk_cuts(ci, ws, end, eof, slot_end + s0, slot_off[f + 1] - s0);
-    first_start[f] = ws;
+    if (f >= a.n_files) return;
+    file_count[f] = (uint32_t)(a.sa.seg_base[a.sa.seg_off[f + 1]] - a.sa.seg_base[a.sa.seg_off[f]]);
+    first_start[f] = a.range_mode ? a.range.walk_start : a.file_off[f];
 }
 
 int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_t st) {
     if (b.n_files == 0) return 0;
-    RangeWalk r{0, 1};
-    if (range) r = *range;
-    const int threads = 32;
-    resolve_files_kernel<<<(b.n_files + threads - 1) / threads, threads, 0, st>>>(
-        b.cand, b.tile_off, b.scalars, b.cand_cap, b.n_tiles, b.file_off, b.slot_off, b.n_files, b.slot_end,
-        b.file_count, b.first_start, r, range != nullptr);
-    return 1;
+    ResolveArgs a{};
+    a.cand = b.cand;
+    a.tile_off = b.tile_off;
+    a.scalars = b.scalars;
+    a.cand_cap = b.cand_cap;
+    a.n_tiles = b.n_tiles;
+    a.file_off = b.file_off;
+    a.n_files = b.n_files;
+    a.n_segs = b.n_segs;
+    a.range = range ? *range : RangeWalk{0, 1};
+    a.range_mode = range != nullptr;
+    a.sa = SegArrays{b.seg_off, b.seg_spec, b.seg_pre, b.seg_spec_n, b.seg_pre_n, b.seg_merge_idx,
+                     b.seg_exit_spec, b.seg_exit_true, b.seg_final_n, b.seg_base};
+    int n = 0;
+    if (b.n_segs) {
+        const unsigned sblocks = (unsigned)((b.n_segs + 63) / 64);
+        resolve_spec_kernel<<<sblocks, 64, 0, st>>>(a);
+        resolve_sync_kernel<<<sblocks, 64, 0, st>>>(a);
+        resolve_fix_kernel<<<(b.n_files * 32 + 127) / 128, 128, 0, st>>>(a);
+        n += 3;
+    }
+    n += launch_scan_u32(b.seg_final_n, b.seg_base, b.n_segs, b.scan_partial, nullptr, st);
+    if (b.n_segs) {
+        resolve_stitch_kernel<<<(unsigned)((b.n_segs * 32 + 127) / 128), 128, 0, st>>>(a, b.slot_off, b.slot_end);
+        n++;
+    }
+    resolve_file_counts_kernel<<<(b.n_files + 127) / 128, 128, 0, st>>>(a, b.file_count, b.first_start);
+    return n + 1;
 }
 
 // ------------------------------------------------------------------------------- bookkeeping

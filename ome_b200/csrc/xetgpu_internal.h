@@ -21,6 +21,11 @@ constexpr int kGearHalo = 64;                                   // bytes staged 
 constexpr int kGearCap = 128;                                   // staged candidates per tile (fast path)
 constexpr int kGearTableCopies = 16;                            // smem replicas of the gear table
 
+// ---- K2 geometry.  Boundary resolution speculates per segment of kSegBytes (>= kMaxChunk, so every
+// full segment holds at least one cut); a segment holds at most kSegBytes/kMinChunk + 1 cuts.
+constexpr uint64_t kSegBytes = 2ull << 20;
+constexpr uint32_t kSegCap = (uint32_t)(kSegBytes / kMinChunk) + 2;
+
 // ---- K3 geometry.  A "group" is up to kLeavesPerGroup consecutive 1 KiB BLAKE3 leaves of one
 // chunk, hashed by one lane, which also merges them into one subtree chaining value.
 constexpr int kLeavesPerGroup = 4;
@@ -47,6 +52,18 @@ struct PipelineBuffers {
     uint32_t* file_count;       // [n_files] chunks per file
     uint64_t* first_start;      // [n_files] absolute start of the first emitted chunk
     uint64_t* file_chunk_base;  // [n_files+1] exclusive scan of file_count
+    // K2 segment speculation (resolve.cu)
+    const uint64_t* seg_off;    // device [n_files+1] first segment of each file
+    uint64_t n_segs;
+    uint64_t* seg_spec;         // [n_segs * kSegCap]
+    uint64_t* seg_pre;          // [n_segs * kSegCap]
+    uint32_t* seg_spec_n;       // [n_segs] ...
+    uint32_t* seg_pre_n;
+    uint32_t* seg_merge_idx;
+    uint32_t* seg_final_n;
+    uint64_t* seg_exit_spec;
+    uint64_t* seg_exit_true;
+    uint64_t* seg_base;         // [n_segs+1]
     // K3
     uint64_t* chunk_start;      // [n_slots] absolute start
     uint32_t* chunk_len;        // [n_slots] 0 = empty slot
@@ -62,6 +79,11 @@ struct PipelineBuffers {
     uint64_t* node_size[2];     // ping-pong [n_slots]
     uint32_t* level_count[2];   // [n_files] nodes per file at the current / next level
     uint32_t* group_start;      // [n_slots] group start indices within a file's level
+    uint64_t* mk_bits;          // [n_slots] per 32-node block: group-end flags of nodes 0..39
+    uint64_t* mk_out;           // [n_slots] per block: exit offset for each of the 9 entry offsets (4 bits each)
+    uint64_t* mk_cnt;           // [n_slots] per block: group starts for each entry offset (5 bits each)
+    uint32_t* mk_entry;         // [n_slots] per block: entry offset of the true chain
+    uint32_t* mk_base;          // [n_slots] per block: group starts before the block
     uint8_t* file_root;         // [n_files * 32]
     uint8_t* file_hash;         // [n_files * 32]
     // dense outputs

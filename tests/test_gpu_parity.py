@@ -97,6 +97,26 @@ def test_ragged_random_files_batch(hasher):
         check_against_oracle(cl, f, d)
 
 
+SEG = 2 << 20   # kSegBytes of the boundary-resolution kernels
+
+
+@pytest.mark.parametrize("spec", [
+    # chains that never re-merge: candidate-free run after an unaligned prefix, across many segments
+    [["splitmix", 61, (1 << 20) + 5], ["zeros", 9 << 20], ["splitmix", 62, 3 << 20]],
+    # dense candidates (every 64 bytes) in the middle of random data
+    [["splitmix", 63, (3 << 20) + 77], ["repeat", xet_inputs.W_HEX, 40000], ["splitmix", 64, 2 << 20]],
+    # file sizes at the segment size and around it
+    [["splitmix", 65, SEG]], [["splitmix", 66, SEG - 1]], [["splitmix", 67, SEG + 1]], [["splitmix", 68, 3 * SEG]],
+    [["zeros", 3 * SEG + 4097]], [["mod251", 2 * SEG + 100]],
+    # forced cuts that straddle a segment end exactly
+    [["zeros", SEG - 131072], ["splitmix", 69, 131072 + 9000]],
+], ids=lambda s: "+".join(f"{seg[0]}{seg[-1]}" for seg in s))
+def test_boundary_speculation_paths(hasher, spec):
+    data = xet_inputs.build(spec)
+    cl = hasher.hash_bytes(data, want_chunks=True)
+    check_against_oracle(cl, 0, data)
+
+
 def test_nonzero_first_offset_and_unaligned_views(hasher):
     data = xet_inputs.splitmix_bytes(77, (3 << 20) + 123)
     for lead in (1, 7, 16, 33):
