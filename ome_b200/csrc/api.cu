@@ -85,6 +85,7 @@ struct XetGpuContext {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     uint32_t flags = 0;
+    uint32_t sm_count = 148;
     uint64_t staging_bytes = 64ull << 20;
     uint64_t max_batch_bytes = 8ull << 30;
     std::mutex mu;
@@ -148,6 +149,7 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
         return make_error(XETGPU_ERR_UNKNOWN, "libxetgpu is built for sm_100a (B200) only", prop.name);
     XetGpuContext* c = new XetGpuContext();
     c->device = dev;
+    c->sm_count = (uint32_t)prop.multiProcessorCount;
     if (config) {
         c->flags = config->flags;
         if (config->staging_bytes) c->staging_bytes = (config->staging_bytes + 4095) & ~4095ull;
@@ -469,7 +471,10 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
         CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
         CU(cudaMemsetAsync(b.scalars, 0, 64, st));
-        launches += launch_gear(b, st);
+        b.sm_count = c->sm_count;
+        cudaError_t gear_err = cudaSuccess;
+        launches += launch_gear(b, st, &gear_err);
+        if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
         if (timing) cudaEventRecord(c->ev[1], st);
         launches += launch_resolve(b, opt.range, st);
         if (timing) cudaEventRecord(c->ev[2], st);
@@ -837,7 +842,10 @@ extern "C" XetError* xetgpu_gear_candidates(XetGpuContext* c, const void* data, 
         if (XetError* e = ensure_workspace(c, plan, &b)) return e;
         b.data = d;
         CU(cudaMemsetAsync(b.scalars, 0, 64, c->stream));
-        launch_gear(b, c->stream);
+        b.sm_count = c->sm_count;
+        cudaError_t gear_err = cudaSuccess;
+        launch_gear(b, c->stream, &gear_err);
+        if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
         CU(cudaGetLastError());
         uint64_t n = 0;
         CU(cudaMemcpyAsync(&n, b.scalars + kScalarCand, 8, cudaMemcpyDeviceToHost, c->stream));

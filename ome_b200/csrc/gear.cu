@@ -8,14 +8,10 @@
 // bytes warms its rolling state on the 64 bytes in front of the strip and is exact from the
 // strip's first byte on.
 //
-// Data movement: one CTA owns a 66 KiB tile.  The tile and the 64-byte halo in front of it are
-// brought into shared memory by bulk TMA copies (cp.async.bulk, completion on an mbarrier — SASS
-// UBLKCP), so no LSU instruction is spent on staging and HBM sees whole, aligned lines exactly once.
-// Each lane then walks its own 528-byte strip with 16-byte LDS; 528 = 33*16 is an odd number of
-// 16-byte bank groups, which makes the 32 strided lane accesses conflict-free.  The gear table
-// lookup is the hot shared-memory access (one 8-byte load per input byte per lane): the table is
-// replicated 16x in shared memory, lane l reading replica l%16, so the 16 lanes of each LDS.64
-// phase always hit 16 distinct bank pairs whatever the data bytes are.
+// Data movement and the table lookup are described at the K1 section below.
+#include <cuda.h>
+#include <string.h>
+
 #include "tma.cuh"
 #include "xetgpu_internal.h"
 #include "../../include/xet_gear_table.h"
@@ -66,116 +62,195 @@ int launch_fill_splitmix(uint8_t* dst, uint64_t seed, uint64_t byte_off, uint64_
 }
 
 // ------------------------------------------------------------------------------------------ K1
-constexpr int kGearTableBytes = 256 * kGearTableCopies * 8;                 // 32 KiB
-constexpr int kGearTileSmem = kGearHalo + kGearTile + 16;                   // staged bytes (+ tail slack)
-constexpr int kGearSmem = kGearTableBytes + kGearTileSmem;
-constexpr int kGearPieces = 4;                                              // bulk copies per tile
+// Geometry: the buffer is viewed as a 2-D tensor of 4 KiB rows.  A warp owns a tile of 32
+// consecutive rows (128 KiB of contiguous bytes); lane l walks row l from left to right.  The rows
+// stream through shared memory as TMA boxes of {128 bytes x 32 rows} (one cp.async.bulk.tensor per
+// box, SASS UTMALDG, 128-byte swizzle), kGearStages boxes in flight per warp behind mbarriers, so
+// HBM latency is hidden by the TMA unit and no LSU instruction is spent on staging.  The 64 bytes
+// in front of every row (the previous row's tail) arrive as one extra box per tile and only warm
+// the rolling hash: 64 / 4096 = 1.6 % overhead.
+constexpr int kGearRow = 4096;
+static_assert(kGearTile == 32 * kGearRow, "a tile is 32 rows");
+constexpr int kGearWarps = 8;
+constexpr int kGearThreads = kGearWarps * 32;
+constexpr int kGearStages = 4;
+constexpr int kGearBox = 32 * 128;                                           // bytes per box
+constexpr int kGearBoxesPerTile = 1 + kGearRow / 128;                        // halo box + 32
+constexpr int kGearTableBytes = 256 * 32 * 8;                                // [byte][lane] u64, 64 KiB
+constexpr int kGearOffStages = kGearTableBytes;
+constexpr int kGearOffLists = kGearOffStages + kGearWarps * kGearStages * kGearBox;
+constexpr int kGearOffBars = kGearOffLists + kGearWarps * kGearCap * 4;
+constexpr int kGearOffCnt = kGearOffBars + kGearWarps * kGearStages * 8;
+constexpr int kGearSmem = kGearOffCnt + kGearWarps * 4 + 1024;               // + slack to align the base to 1 KiB
 
-// Stage tile `tile` (and its halo) in s_tile; s_tile[0] corresponds to absolute byte
-// tile_start - kGearHalo.  Returns the number of valid tile bytes.  All threads call it.
-__device__ __forceinline__ uint32_t gear_load_tile(const uint8_t* __restrict__ data, uint64_t total, uint32_t tile,
-                                                   uint8_t* s_tile, uint64_t* bar, uint32_t parity) {
-    const uint64_t tile_start = (uint64_t)tile * kGearTile;
-    const uint64_t src_begin = tile ? tile_start - kGearHalo : 0;
-    const uint32_t dst_off = tile ? 0 : kGearHalo;
-    uint64_t tile_end = tile_start + kGearTile;
-    if (tile_end > total) tile_end = total;
-    const uint32_t avail = (uint32_t)(tile_end - src_begin);
-    const uint32_t bulk = avail & ~15u;
-    if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(bar, bulk);
-        constexpr uint32_t piece = (kGearTile / kGearPieces);  // 16,896 B, a multiple of 16
-        for (uint32_t o = 0; o < bulk; o += piece) {
-            uint32_t n = bulk - o < piece ? bulk - o : piece;
-            tma_bulk_g2s(s_tile + dst_off + o, data + src_begin + o, n, bar);
-        }
-    }
-    // bytes that do not fill a 16-byte unit at the end of the buffer, and the zero halo of tile 0
-    if (threadIdx.x < avail - bulk) s_tile[dst_off + bulk + threadIdx.x] = data[src_begin + bulk + threadIdx.x];
-    if (tile == 0 && threadIdx.x < kGearHalo / 4) reinterpret_cast<uint32_t*>(s_tile)[threadIdx.x] = 0u;
-    mbar_wait(bar, parity);
-    __syncthreads();
-    return (uint32_t)(tile_end - tile_start);
+__device__ __forceinline__ void tma_box_g2s(void* dst_smem, const CUtensorMap* tmap, int32_t c0, int32_t c1,
+                                            uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
 }
 
+// The table is laid out [byte value][lane] so that one PRMT builds the whole shared-memory offset
+// (byte << 8) | (lane * 8), and the 16 lanes of each LDS.64 phase hit 16 distinct bank pairs.
 __device__ __forceinline__ void gear_load_table(uint64_t* s_table) {
-    for (int i = threadIdx.x; i < 256 * kGearTableCopies; i += blockDim.x) s_table[i] = c_gear[i / kGearTableCopies];
+    for (int i = threadIdx.x; i < 256 * 32; i += blockDim.x) s_table[i] = c_gear[i >> 5];
 }
 
-// Walk one strip: 64 warm-up bytes, then kGearStrip tested bytes.  `on_match(pos)` is called with
-// the tile-relative position of every candidate below `valid`.
+struct GearLane {
+    uint32_t tab;     // shared-memory address of the table
+    uint32_t lane8;   // lane * 8
+    uint64_t h;       // rolling hash
+};
+
+template <int J>
+__device__ __forceinline__ uint64_t gear_lookup(const GearLane& g, uint32_t w) {
+    // bytes of the result: [0] = lane*8, [1] = byte J of w, [2] = [3] = 0  ->  (byte << 8) | lane*8
+    const uint32_t off = __byte_perm(w, g.lane8, 0x5504 | (J << 4));
+    uint64_t v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(g.tab + off));
+    return v;
+}
+
+// 16 bytes: roll, and report through on_match every position (base + j) whose hash is a candidate.
+template <bool kTest, typename F>
+__device__ __forceinline__ void gear_chunk16(GearLane& g, uint4 v, uint32_t base, F on_match) {
+    uint64_t t[16];
+    t[0] = gear_lookup<0>(g, v.x); t[1] = gear_lookup<1>(g, v.x); t[2] = gear_lookup<2>(g, v.x); t[3] = gear_lookup<3>(g, v.x);
+    t[4] = gear_lookup<0>(g, v.y); t[5] = gear_lookup<1>(g, v.y); t[6] = gear_lookup<2>(g, v.y); t[7] = gear_lookup<3>(g, v.y);
+    t[8] = gear_lookup<0>(g, v.z); t[9] = gear_lookup<1>(g, v.z); t[10] = gear_lookup<2>(g, v.z); t[11] = gear_lookup<3>(g, v.z);
+    t[12] = gear_lookup<0>(g, v.w); t[13] = gear_lookup<1>(g, v.w); t[14] = gear_lookup<2>(g, v.w); t[15] = gear_lookup<3>(g, v.w);
+    const uint64_t h0 = g.h;
+    uint64_t h = h0;
+    bool hit = false;
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        h = (h << 1) + t[j];
+        if (kTest) hit |= (uint32_t)(h >> 32) < (1u << (32 - kTopBits));
+    }
+    g.h = h;
+    if (kTest && hit) {  // rare (2^-12 per chunk on random data): replay to find the positions
+        uint64_t r = h0;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            r = (r << 1) + t[j];
+            if ((uint32_t)(r >> 32) < (1u << (32 - kTopBits))) on_match(base + j);
+        }
+    }
+}
+
+// Bytes that are not part of a full 4 KiB row (the end of the buffer): plain global loads.
 template <typename F>
-__device__ __forceinline__ void gear_strip(const uint8_t* s_tile, const uint64_t* s_table, uint32_t valid, F on_match) {
-    const uint32_t strip_first = threadIdx.x * kGearStrip;  // tile-relative position of first tested byte
-    if (strip_first >= valid) return;
-    const uint64_t* tab = s_table + (threadIdx.x & (kGearTableCopies - 1));
-    const uint4* src = reinterpret_cast<const uint4*>(s_tile + strip_first);  // halo makes this strip_first - 64
+__device__ __forceinline__ void gear_slow_span(const uint8_t* __restrict__ data, const uint64_t* s_table,
+                                               uint32_t tab_stride, uint32_t lane, uint64_t begin, uint64_t end,
+                                               uint32_t pos0, F on_match) {
+    if (begin >= end) return;
     uint64_t h = 0;
-#pragma unroll 1
-    for (int k = 0; k < kGearHalo / 16; k++) {
-        uint4 v = src[k];
-        uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            uint32_t b = (w[j >> 2] >> (8 * (j & 3))) & 0xffu;
-            h = (h << 1) + tab[b * kGearTableCopies];
-        }
-    }
-#pragma unroll 1
-    for (int k = 0; k < kGearStrip / 16; k++) {
-        uint4 v = src[kGearHalo / 16 + k];
-        uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            uint32_t b = (w[j >> 2] >> (8 * (j & 3))) & 0xffu;
-            h = (h << 1) + tab[b * kGearTableCopies];
-            if ((uint32_t)(h >> 32) < (1u << (32 - kTopBits))) {
-                uint32_t pos = strip_first + k * 16 + j;
-                if (pos < valid) on_match(pos);
-            }
-        }
+    for (uint64_t i = begin >= 64 ? begin - 64 : 0; i < end; i++) {
+        h = (h << 1) + s_table[(uint32_t)data[i] * tab_stride + lane];
+        if (i >= begin && (uint32_t)(h >> 32) < (1u << (32 - kTopBits))) on_match(pos0 + (uint32_t)(i - begin));
     }
 }
 
-// Pass 1 over every tile: count candidates, stage up to kGearCap of them in ascending order.
-__global__ void __launch_bounds__(kGearThreads)
-    gear_scan_kernel(const uint8_t* __restrict__ data, uint64_t total, uint32_t* __restrict__ tile_count,
+// Pass 1: count candidates per tile and stage up to kGearCap of them in ascending order.
+__global__ void __launch_bounds__(kGearThreads, 1)
+    gear_scan_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __restrict__ data, uint64_t total,
+                     uint64_t rows, uint32_t n_tiles, uint32_t* __restrict__ tile_count,
                      uint32_t* __restrict__ tile_stage) {
-    extern __shared__ __align__(128) uint8_t smem[];
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* s_table = reinterpret_cast<uint64_t*>(smem);
-    uint8_t* s_tile = smem + kGearTableBytes;
-    __shared__ __align__(8) uint64_t s_bar;
-    __shared__ uint32_t s_n;
-    __shared__ uint32_t s_list[kGearCap];
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    uint8_t* stages = smem + kGearOffStages + wid * (kGearStages * kGearBox);
+    uint32_t* s_list = reinterpret_cast<uint32_t*>(smem + kGearOffLists) + wid * kGearCap;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGearOffBars) + wid * kGearStages;
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem + kGearOffCnt) + wid;
 
-    if (threadIdx.x == 0) {
-        mbar_init(&s_bar, 1);
-        mbar_fence_init();
-        s_n = 0;
-    }
     gear_load_table(s_table);
+    if (lane == 0) {
+        for (int i = 0; i < kGearStages; i++) mbar_init(&bars[i], 1);
+        mbar_fence_init();
+        *s_cnt = 0;
+    }
     __syncthreads();
-    const uint32_t tile = blockIdx.x;
-    const uint32_t valid = gear_load_tile(data, total, tile, s_tile, &s_bar, 0);
 
-    gear_strip(s_tile, s_table, valid, [&](uint32_t pos) {
-        uint32_t slot = atomicAdd(&s_n, 1u);
+    GearLane g;
+    g.tab = smem_u32(s_table);
+    g.lane8 = lane * 8u;
+    auto emit = [&](uint32_t pos) {
+        const uint32_t slot = atomicAdd(s_cnt, 1u);
         if (slot < kGearCap) s_list[slot] = pos;
-    });
-    __syncthreads();
-    const uint32_t n = s_n;
-    if (threadIdx.x == 0) tile_count[tile] = n;
-    if (n <= kGearCap && threadIdx.x < n) {  // rank sort (positions are distinct)
-        const uint32_t mine = s_list[threadIdx.x];
-        uint32_t rank = 0;
-        for (uint32_t j = 0; j < n; j++) rank += s_list[j] < mine;
-        tile_stage[(uint64_t)tile * kGearCap + rank] = mine;
+    };
+    const uint32_t swz = lane & 7u;
+    uint32_t q = 0;  // boxes this warp has consumed so far: stage = q % kGearStages, parity = (q / kGearStages) & 1
+
+    for (uint32_t tile = blockIdx.x * kGearWarps + wid; tile < n_tiles; tile += gridDim.x * kGearWarps) {
+        const uint64_t row0 = (uint64_t)tile * 32u;
+        const bool row_valid = row0 + lane < rows;
+        if (row0 < rows) {
+            auto issue = [&](uint32_t bi) {  // box bi of this tile into stage (q0 + bi) % kGearStages
+                uint64_t* bar = &bars[(q + bi) % kGearStages];
+                mbar_arrive_expect_tx(bar, kGearBox);
+                if (bi == 0) tma_box_g2s(stages + ((q + bi) % kGearStages) * kGearBox, &tmap, kGearRow - 128, (int32_t)row0 - 1, bar);
+                else tma_box_g2s(stages + ((q + bi) % kGearStages) * kGearBox, &tmap, (int32_t)(bi - 1) * 128, (int32_t)row0, bar);
+            };
+            if (lane == 0)
+                for (uint32_t bi = 0; bi < kGearStages; bi++) issue(bi);
+            g.h = 0;
+#pragma unroll 1
+            for (uint32_t bi = 0; bi < kGearBoxesPerTile; bi++) {
+                const uint32_t st = (q + bi) % kGearStages;
+                mbar_wait(&bars[st], ((q + bi) / kGearStages) & 1u);
+                const uint8_t* rowp = stages + st * kGearBox + lane * 128u;
+                if (row_valid) {
+                    if (bi == 0) {  // the 64 bytes in front of the row: warm-up only
+#pragma unroll
+                        for (uint32_t c = 4; c < 8; c++)
+                            gear_chunk16<false>(g, *reinterpret_cast<const uint4*>(rowp + ((c ^ swz) << 4)), 0u, emit);
+                    } else {
+                        const uint32_t pos = lane * kGearRow + (bi - 1) * 128u;
+#pragma unroll 2
+                        for (uint32_t c = 0; c < 8; c++)
+                            gear_chunk16<true>(g, *reinterpret_cast<const uint4*>(rowp + ((c ^ swz) << 4)), pos + c * 16u, emit);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0 && bi + kGearStages < kGearBoxesPerTile) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    issue(bi + kGearStages);
+                }
+            }
+            q += kGearBoxesPerTile;
+        }
+        // the partial last row of the buffer, if it lies in this tile: 128-byte pieces, one per lane
+        if (rows >= row0 && rows < row0 + 32u && total > rows * kGearRow) {
+            const uint64_t tb = rows * kGearRow;
+            const uint64_t b0 = tb + lane * 128u;
+            const uint64_t b1 = b0 + 128u < total ? b0 + 128u : total;
+            gear_slow_span(data, s_table, 32u, lane, b0, b1, (uint32_t)(rows - row0) * kGearRow + lane * 128u, emit);
+        }
+        __syncwarp();
+        const uint32_t n = *s_cnt;
+        if (lane == 0) tile_count[tile] = n;
+        if (n <= kGearCap)
+            for (uint32_t i = lane; i < n; i += 32) {  // rank sort (positions are distinct)
+                const uint32_t mine = s_list[i];
+                uint32_t rank = 0;
+                for (uint32_t j = 0; j < n; j++) rank += s_list[j] < mine;
+                tile_stage[(uint64_t)tile * kGearCap + rank] = mine;
+            }
+        __syncwarp();
+        if (lane == 0) *s_cnt = 0;
+        __syncwarp();
     }
 }
 
-// Pass 2: move staged candidates to their final place; tiles that overflowed the stage (dense
-// candidates — adversarial data only) are recomputed with an ordered two-sweep emission.
-__global__ void __launch_bounds__(kGearThreads)
+// Pass 2: move staged candidates to their final place.  A tile that overflowed its stage (dense
+// candidates — adversarial data only) is recomputed here with an ordered two-sweep emission, one
+// 1 KiB piece per thread, straight from global memory.
+constexpr int kCompactThreads = 128;
+__global__ void __launch_bounds__(kCompactThreads)
     gear_compact_kernel(const uint8_t* __restrict__ data, uint64_t total, const uint32_t* __restrict__ tile_count,
                         const uint32_t* __restrict__ tile_stage, const uint64_t* __restrict__ tile_off,
                         uint64_t* __restrict__ cand, uint64_t cand_cap) {
@@ -189,27 +264,24 @@ __global__ void __launch_bounds__(kGearThreads)
             cand[base + threadIdx.x] = tile_start + tile_stage[(uint64_t)tile * kGearCap + threadIdx.x];
         return;
     }
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* s_table = reinterpret_cast<uint64_t*>(smem);
-    uint8_t* s_tile = smem + kGearTableBytes;
-    __shared__ __align__(8) uint64_t s_bar;
-    __shared__ uint32_t s_cnt[kGearThreads];
-    if (threadIdx.x == 0) {
-        mbar_init(&s_bar, 1);
-        mbar_fence_init();
-    }
-    gear_load_table(s_table);
+    __shared__ uint64_t s_tab[256];
+    __shared__ uint32_t s_cnt[kCompactThreads];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_tab[i] = c_gear[i];
     __syncthreads();
-    const uint32_t valid = gear_load_tile(data, total, tile, s_tile, &s_bar, 0);
+    constexpr uint32_t piece = kGearTile / kCompactThreads;  // 1 KiB
+    uint64_t b0 = tile_start + threadIdx.x * piece;
+    uint64_t b1 = b0 + piece;
+    if (b0 > total) b0 = total;
+    if (b1 > total) b1 = total;
     uint32_t mine = 0;
-    gear_strip(s_tile, s_table, valid, [&](uint32_t) { mine++; });
+    gear_slow_span(data, s_tab, 1u, 0u, b0, b1, 0u, [&](uint32_t) { mine++; });
     s_cnt[threadIdx.x] = mine;
     __syncthreads();
     uint32_t before = 0;
     for (uint32_t j = 0; j < threadIdx.x; j++) before += s_cnt[j];
     uint64_t w = base + before;
-    gear_strip(s_tile, s_table, valid, [&](uint32_t pos) {
-        if (w < cand_cap) cand[w] = tile_start + pos;
+    gear_slow_span(data, s_tab, 1u, 0u, b0, b1, 0u, [&](uint32_t pos) {
+        if (w < cand_cap) cand[w] = b0 + pos;
         w++;
     });
 }
@@ -304,21 +376,62 @@ int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* par
 // Called once per context with its device current (function attributes are per device).
 void init_gear_kernels() {
     cudaFuncSetAttribute(gear_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGearSmem);
-    cudaFuncSetAttribute(gear_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGearSmem);
 }
 
-int launch_gear(const PipelineBuffers& b, cudaStream_t st) {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &p, 12000, cudaEnableDefault, &qres) ==
+                cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+int launch_gear(const PipelineBuffers& b, cudaStream_t st, cudaError_t* err) {
+    *err = cudaSuccess;
     if (b.n_tiles == 0) {
         cudaMemsetAsync(b.tile_off, 0, sizeof(uint64_t), st);
         cudaMemsetAsync(b.scalars + kScalarCand, 0, sizeof(uint64_t), st);
         return 0;
     }
+    const uint64_t rows = b.total_bytes / kGearRow;
+    alignas(64) CUtensorMap tmap;
+    memset(&tmap, 0, sizeof tmap);
+    if (rows) {
+        EncodeTiledFn enc = encode_tiled_fn();
+        if (!enc) {
+            *err = cudaErrorSymbolNotFound;
+            return 0;
+        }
+        const cuuint64_t gdim[2] = {kGearRow, rows};
+        const cuuint64_t gstride[1] = {kGearRow};
+        const cuuint32_t box[2] = {128, 32};
+        const cuuint32_t estride[2] = {1, 1};
+        CUresult r = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)b.data, gdim, gstride, box, estride,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            *err = cudaErrorInvalidValue;
+            return 0;
+        }
+    }
+    unsigned ctas = (b.n_tiles + kGearWarps - 1) / kGearWarps;
+    if (ctas > b.sm_count) ctas = b.sm_count;
     if (b.ev_kernel[0]) cudaEventRecord(b.ev_kernel[0], st);
-    gear_scan_kernel<<<b.n_tiles, kGearThreads, kGearSmem, st>>>(b.data, b.total_bytes, b.tile_count, b.tile_stage);
+    gear_scan_kernel<<<ctas, kGearThreads, kGearSmem, st>>>(tmap, b.data, b.total_bytes, rows, b.n_tiles, b.tile_count,
+                                                            b.tile_stage);
     if (b.ev_kernel[1]) cudaEventRecord(b.ev_kernel[1], st);
     int n = 1 + launch_scan_u32(b.tile_count, b.tile_off, b.n_tiles, b.scan_partial, b.scalars + kScalarCand, st);
-    gear_compact_kernel<<<b.n_tiles, kGearThreads, kGearSmem, st>>>(b.data, b.total_bytes, b.tile_count, b.tile_stage,
-                                                                    b.tile_off, b.cand, b.cand_cap);
+    gear_compact_kernel<<<b.n_tiles, kCompactThreads, 0, st>>>(b.data, b.total_bytes, b.tile_count, b.tile_stage,
+                                                               b.tile_off, b.cand, b.cand_cap);
     return n + 1;
 }
 

@@ -11,15 +11,10 @@ constexpr uint32_t kMinChunk = 8192;
 constexpr uint32_t kMaxChunk = 131072;
 constexpr uint32_t kTopBits = 16;  // MASK = 0xFFFF000000000000: the 16 top bits must be clear
 
-// ---- K1 geometry.  One CTA owns a tile of kGearThreads strips of kGearStrip bytes.  The strip
-// length is an ODD multiple of 16 bytes so that the 32 lanes of a warp, each reading 16 bytes of
-// its own strip, touch 32 distinct 16-byte bank groups (conflict-free LDS.128).
-constexpr int kGearThreads = 128;
-constexpr int kGearStrip = 528;                                 // 33 * 16
-constexpr int kGearTile = kGearThreads * kGearStrip;            // 67,584 bytes
-constexpr int kGearHalo = 64;                                   // bytes staged in front of the tile
-constexpr int kGearCap = 128;                                   // staged candidates per tile (fast path)
-constexpr int kGearTableCopies = 16;                            // smem replicas of the gear table
+// ---- K1 geometry (gear.cu).  A tile is the 128 KiB of contiguous bytes one warp scans per step:
+// 32 rows of 4 KiB, one row per lane.  Candidates are staged per tile.
+constexpr int kGearTile = 131072;
+constexpr int kGearCap = 128;     // staged candidates per tile (fast path; expected ~2)
 
 // ---- K2 geometry.  Boundary resolution speculates per segment of kSegBytes (>= kMaxChunk, so every
 // full segment holds at least one cut); a segment holds at most kSegBytes/kMinChunk + 1 cuts.
@@ -93,6 +88,7 @@ struct PipelineBuffers {
     uint64_t* scan_partial;     // [scan_blocks_cap]
     uint64_t* scalars;          // [8] device scalars: 0 = n_cand, 1 = n_groups, 2 = n_chunks
     uint32_t max_levels;        // host bound on merkle depth
+    uint32_t sm_count;          // SMs of the device (persistent-kernel grid size)
     // optional timing events (nullptr = off): [0,1] around gear_scan_kernel, [2,3] around leaf_group_kernel
     cudaEvent_t ev_kernel[4];
 };
@@ -101,7 +97,7 @@ enum { kScalarCand = 0, kScalarGroups = 1, kScalarChunks = 2, kScalarFlags = 3 }
 
 // Launchers (all asynchronous on `st`); each returns the number of kernels it launched.
 int launch_fill_splitmix(uint8_t* dst, uint64_t seed, uint64_t byte_off, uint64_t len, cudaStream_t st);
-int launch_gear(const PipelineBuffers& b, cudaStream_t st);
+int launch_gear(const PipelineBuffers& b, cudaStream_t st, cudaError_t* err);
 // Range mode (one "file" that is a byte range of a larger file): the walk starts at the absolute
 // position walk_start, the buffer end is NOT the end of the file unless is_eof, and the walk stops at
 // the first cut beyond the buffer.  Whole-file mode: walk_start is ignored (range == nullptr).
