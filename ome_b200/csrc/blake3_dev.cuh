@@ -31,16 +31,30 @@ __device__ __forceinline__ uint32_t rotr8(uint32_t x) { return __byte_perm(x, 0,
 __device__ __forceinline__ uint32_t rotr12(uint32_t x) { return __funnelshift_r(x, x, 12); }
 __device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x, x, 7); }
 
-#define XG_G(a, b, c, d, mx, my) \
-    do {                         \
-        a = a + b + (mx);        \
-        d = rotr16(d ^ a);       \
-        c = c + d;               \
-        b = rotr12(b ^ c);       \
-        a = a + b + (my);        \
-        d = rotr8(d ^ a);        \
-        c = c + d;               \
-        b = rotr7(b ^ c);        \
+// Pipe balance (measured on B200, profiles/r1_int_pipes.txt): LOP3/SHF/PRMT/IADD3 issue on the ALU
+// pipe at 64 lanes/clk/SM, IMAD on the FMA pipe at another 64 lanes/clk/SM, and the two overlap.
+// A G function is 4 xors + 4 rotates (ALU only) + 6 additions; writing every addition as
+// x * 1 + y with a multiplier the assembler cannot see through (a __constant__ it must load) keeps
+// all eight two-input additions on the FMA pipe: 8 ALU + 8 FMA slots per G instead of 10 + 2.
+// (a + m) is formed first — it does not wait for b — so the dependent chain per G stays 12 deep.
+static __constant__ uint32_t c_b3_one = 1u;
+
+__device__ __forceinline__ uint32_t fma_add(uint32_t x, uint32_t y, uint32_t one) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(one), "r"(y));
+    return r;
+}
+
+#define XG_G(a, b, c, d, mx, my)              \
+    do {                                      \
+        a = fma_add(fma_add(a, (mx), one), b, one); \
+        d = rotr16(d ^ a);                    \
+        c = fma_add(c, d, one);               \
+        b = rotr12(b ^ c);                    \
+        a = fma_add(fma_add(a, (my), one), b, one); \
+        d = rotr8(d ^ a);                     \
+        c = fma_add(c, d, one);               \
+        b = rotr7(b ^ c);                     \
     } while (0)
 
 // One round with message word indices given as literals.
@@ -65,6 +79,7 @@ __device__ __forceinline__ void b3_compress(uint32_t (&cv)[8], const uint32_t (&
     uint32_t v4 = cv[4], v5 = cv[5], v6 = cv[6], v7 = cv[7];
     uint32_t v8 = XG_IV0, v9 = XG_IV1, v10 = XG_IV2, v11 = XG_IV3;
     uint32_t v12 = counter_lo, v13 = counter_hi, v14 = block_len, v15 = flags;
+    const uint32_t one = c_b3_one;
     // message schedule = repeated application of the BLAKE3 permutation
     XG_ROUND(0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15);
     XG_ROUND(2, 6, 3, 10, 7, 0, 4, 13, 1, 11, 12, 5, 9, 14, 15, 8);

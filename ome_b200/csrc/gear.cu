@@ -123,14 +123,14 @@ __device__ __forceinline__ void gear_chunk16(GearLane& g, uint4 v, uint32_t base
     t[12] = gear_lookup<0>(g, v.w); t[13] = gear_lookup<1>(g, v.w); t[14] = gear_lookup<2>(g, v.w); t[15] = gear_lookup<3>(g, v.w);
     const uint64_t h0 = g.h;
     uint64_t h = h0;
-    bool hit = false;
+    uint32_t lowest = 0xffffffffu;  // min over the 16 positions of the hash's high word: one ALU op per byte
 #pragma unroll
     for (int j = 0; j < 16; j++) {
         h = (h << 1) + t[j];
-        if (kTest) hit |= (uint32_t)(h >> 32) < (1u << (32 - kTopBits));
+        if (kTest) lowest = min(lowest, (uint32_t)(h >> 32));
     }
     g.h = h;
-    if (kTest && hit) {  // rare (2^-12 per chunk on random data): replay to find the positions
+    if (kTest && lowest < (1u << (32 - kTopBits))) {  // rare (2^-12 per chunk on random data): replay for positions
         uint64_t r = h0;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
