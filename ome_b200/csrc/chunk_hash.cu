@@ -10,12 +10,14 @@
 // 2-level subtree merge in registers.  All 32 lanes of a warp do identical work except at chunk
 // tails.  The few remaining tree levels (<= 32 group values per chunk) are folded by K3b.
 //
-// Data movement.  A lane's leaf is 1 KiB at an arbitrary byte address.  Before each leaf round
-// every lane issues ONE bulk TMA copy (cp.async.bulk -> UBLKCP) of the 16-byte-aligned span that
-// covers its leaf into its own 1040-byte row of the warp's shared-memory stage; completion is
-// signalled on a per-warp mbarrier.  No LSU instruction is spent on staging and HBM lines are
-// read once.  Message words are then read with LDS.32 from the row (row stride 1040 B: lanes
-// l, l+8, l+16, l+24 share a bank — a 4-way conflict that costs 68 of the ~1400 issue cycles of a
+// Data movement.  A lane's leaf is 1 KiB at an arbitrary byte address.  It is staged half a leaf
+// (512 bytes, 8 blocks) at a time: every lane issues ONE bulk TMA copy (cp.async.bulk -> UBLKCP)
+// of the 16-byte-aligned span that covers its half leaf into its own 528-byte row of the warp's
+// shared-memory stage; completion is signalled on a per-warp mbarrier.  No LSU instruction is
+// spent on staging and HBM lines are read once.  The small stage (16.5 KiB per warp) is what lets
+// 12 warps share an SM — the compression chains are latency-bound below ~3 warps per scheduler.
+// Message words are read with LDS.32 from the row (row stride 528 B = 132 words: lanes l, l+8,
+// l+16, l+24 share a bank — a 4-way conflict that costs ~68 of the ~1000 issue cycles of a
 // compression) and realigned with one funnel shift per word for the chunk's byte offset.
 #include "blake3_dev.cuh"
 #include "tma.cuh"
@@ -30,29 +32,31 @@ constexpr int kLeafThreads = kLeafWarpsPerCta * 32;
 constexpr int kLeafStage = 32 * kLeafRow;                       // bytes of shared memory per warp
 constexpr int kLeafSmem = kLeafWarpsPerCta * kLeafStage;
 
-// Hash one staged leaf (<= 1024 bytes, at byte `off` of the lane's row) into `cv`.
-__device__ __forceinline__ void hash_leaf(const uint32_t* __restrict__ row, uint32_t off, uint32_t leaf_len,
-                                          uint32_t leaf_index, bool active, bool root_leaf, const uint32_t (&key)[8],
-                                          uint32_t (&cv)[8]) {
-    const uint32_t nb = leaf_len <= 64 ? 1u : (leaf_len + 63u) / 64u;
+// Compress the (up to 8) 64-byte blocks of one staged half leaf into cv.
+//   row      : the lane's shared-memory row (16-byte aligned copy of the aligned span)
+//   off      : byte offset of the first byte of this half inside the row (0..15)
+//   b0       : index of the half's first block inside the leaf (0 or 8)
+//   nb       : blocks in the whole leaf;  leaf_len : bytes in the whole leaf
+__device__ __forceinline__ void hash_half_leaf(const uint32_t* __restrict__ row, uint32_t off, uint32_t b0, uint32_t nb,
+                                               uint32_t leaf_len, uint32_t leaf_index, bool active, bool root_leaf,
+                                               uint32_t (&cv)[8]) {
     const uint32_t shift = (off & 3u) * 8u;
     const uint32_t* wrow = row + (off >> 2);
-#pragma unroll
-    for (int i = 0; i < 8; i++) cv[i] = key[i];
 #pragma unroll 1
-    for (uint32_t b = 0; b < 16; b++) {
+    for (uint32_t k = 0; k < kLeafHalfBlocks; k++) {
+        const uint32_t b = b0 + k;
         const bool go = active && b < nb;
         if (!__any_sync(0xffffffffu, go)) break;
         if (go) {
             uint32_t w[17];
 #pragma unroll
-            for (int i = 0; i < 17; i++) w[i] = wrow[b * 16 + i];
+            for (int i = 0; i < 17; i++) w[i] = wrow[k * 16 + i];
             uint32_t m[16];
 #pragma unroll
             for (int i = 0; i < 16; i++) m[i] = __funnelshift_r(w[i], w[i + 1], shift);
             uint32_t bl = 64;
             if (b == nb - 1) {
-                bl = leaf_len - b * 64;  // 0..64 (0 only for an empty input, which K2 never emits)
+                bl = leaf_len - b * 64;  // 1..64 (a leaf is never empty: K2 emits no empty chunk)
                 if (bl < 64) {
 #pragma unroll
                     for (int i = 0; i < 16; i++) {
@@ -85,7 +89,7 @@ __global__ void __launch_bounds__(kLeafThreads)
     uint64_t* bar = &s_bar[wid];
     if (lane == 0) {
         mbar_init(bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_fence_init();
     }
     __syncwarp();
     uint8_t* stage = smem + wid * kLeafStage;
@@ -112,21 +116,30 @@ __global__ void __launch_bounds__(kLeafThreads)
     for (uint32_t li = 0; li < kLeavesPerGroup; li++) {
         const bool active = valid && li < gleaves;
         if (!__any_sync(0xffffffffu, active)) break;
-        const uint64_t src = cstart + goff + li * 1024u;
         const uint32_t llen = active ? (glen - li * 1024u < 1024u ? glen - li * 1024u : 1024u) : 0u;
-        const uint32_t off = (uint32_t)(src & 15u);
-        const uint32_t copy = active ? ((off + llen + 15u) & ~15u) : 0u;
-        // stage this round's 32 leaves: one bulk copy per lane, one mbarrier phase per round
-        const uint32_t tx = __reduce_add_sync(0xffffffffu, copy);
-        if (lane == 0) mbar_arrive_expect_tx(bar, tx);
-        __syncwarp();
-        if (copy) tma_bulk_g2s(my_row, data + (src - off), copy, bar);
-        mbar_wait(bar, parity);
-        parity ^= 1u;
-
-        hash_leaf(reinterpret_cast<const uint32_t*>(my_row), off, llen, goff / 1024u + li, active,
-                  /*root_leaf=*/cleaves == 1u, key, cv);
-        __syncwarp();  // all lanes are done reading the stage before the next round overwrites it
+        const uint32_t nb = llen <= 64u ? 1u : (llen + 63u) / 64u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) cv[i] = key[i];
+#pragma unroll 1
+        for (uint32_t half = 0; half < 1024u / kLeafHalfBytes; half++) {
+            // stage this half leaf of all 32 lanes: one bulk copy per lane, one mbarrier phase
+            const uint32_t hbeg = half * kLeafHalfBytes;
+            const bool hact = active && (hbeg < llen || half == 0);
+            if (!__any_sync(0xffffffffu, hact)) break;
+            const uint32_t hlen = hact ? (llen - hbeg < kLeafHalfBytes ? llen - hbeg : kLeafHalfBytes) : 0u;
+            const uint64_t src = cstart + goff + li * 1024u + hbeg;
+            const uint32_t off = (uint32_t)(src & 15u);
+            const uint32_t copy = hact ? ((off + hlen + 15u) & ~15u) : 0u;
+            const uint32_t tx = __reduce_add_sync(0xffffffffu, copy);
+            if (lane == 0) mbar_arrive_expect_tx(bar, tx);
+            __syncwarp();
+            if (copy) tma_bulk_g2s(my_row, data + (src - off), copy, bar);
+            mbar_wait(bar, parity);
+            parity ^= 1u;
+            hash_half_leaf(reinterpret_cast<const uint32_t*>(my_row), off, half * kLeafHalfBlocks, nb, llen,
+                           goff / 1024u + li, hact, /*root_leaf=*/cleaves == 1u, cv);
+            __syncwarp();  // all lanes are done reading the stage before the next copy overwrites it
+        }
 
         if (active) {
             if (li == 0) {
