@@ -257,7 +257,7 @@ struct Plan {
     uint32_t n_tiles = 0;
     uint64_t n_groups_cap = 0;
     uint64_t cand_cap = 0;
-    uint32_t max_levels = 0;
+    uint64_t max_nodes = 0;
     std::vector<uint64_t> slot_off;  // host prefix
     std::vector<uint64_t> seg_off;   // host prefix of per-file segment counts (K2)
     uint64_t n_segs = 0;
@@ -295,9 +295,7 @@ static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, u
     p.n_tiles = (uint32_t)((total + kGearTile - 1) / kGearTile);
     p.n_groups_cap = total / (kLeavesPerGroup * 1024ull) + s;
     p.cand_cap = std::max<uint64_t>(std::max<uint64_t>(total / 1024 + 4096, cand_cap_hint), 1);
-    // every group but the last has >= 3 children, so a level of m nodes yields <= (m + 2) / 3 nodes
-    p.max_levels = 1;
-    for (uint64_t m = max_slots; m > 1; m = (m + 2) / 3) p.max_levels++;
+    p.max_nodes = max_slots;
     return p;
 }
 
@@ -311,7 +309,7 @@ static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool
     b->n_tiles = p.n_tiles;
     b->n_groups_cap = p.n_groups_cap;
     b->cand_cap = p.cand_cap;
-    b->max_levels = p.max_levels;
+    b->max_nodes = p.max_nodes;
     b->total_bytes = p.total;
     b->file_off = a.take<uint64_t>(F + 1);
     b->slot_off = a.take<uint64_t>(F + 1);
@@ -926,8 +924,7 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
     plan.n_tiles = 0;
     plan.n_groups_cap = 1;
     plan.cand_cap = 1;
-    plan.max_levels = 1;
-    for (uint64_t m = n_chunks + 1; m > 1; m = (m + 2) / 3) plan.max_levels++;
+    plan.max_nodes = n_chunks + 1;
     PipelineBuffers b{};
     if (XetError* e = ensure_workspace(c, plan, &b)) return e;
     cudaStream_t st = c->stream;

@@ -144,16 +144,104 @@ __device__ __forceinline__ uint32_t file_of_slot_m(const uint64_t* __restrict__ 
     return lo;
 }
 
-struct MsgBuf {
-    uint32_t w[208];  // 832 bytes >= 801
-    uint32_t len;
-    __device__ __forceinline__ void put(uint32_t byte) {
-        w[len >> 2] |= byte << (8u * (len & 3u));
-        len++;
+// ---- node message formatting ------------------------------------------------------------------
+// A node's message is the concatenation of "{hex(hash)} : {size}\n" over its children, hex being
+// MerkleHash::hex (four LE u64 words as %016x).  It is produced four characters at a
+// time: two hash bytes are spread into four nibbles with two byte permutes, turned into ASCII with
+// a SIMD-within-register adjust, and appended through a 64-bit packer that emits whole 32-bit
+// message words — so the buffer needs no zero initialisation and no read-modify-write.
+struct Packer {
+    uint32_t* w;
+    uint32_t n;     // words emitted
+    uint64_t acc;   // pending bytes, little endian
+    uint32_t pend;  // number of pending bytes (0..3)
+    __device__ __forceinline__ void put(uint32_t bytes_le, uint32_t k) {  // k = 1..4 valid bytes, rest zero
+        acc |= (uint64_t)bytes_le << (8u * pend);
+        pend += k;
+        if (pend >= 4u) {
+            w[n++] = (uint32_t)acc;
+            acc >>= 32;
+            pend -= 4u;
+        }
     }
+    __device__ __forceinline__ uint32_t bytes() const { return n * 4u + pend; }
 };
 
-__device__ __forceinline__ uint32_t hex_digit(uint32_t v) { return v < 10 ? '0' + v : 'a' + (v - 10); }
+// Four hex digits of the 16-bit value t (most significant nibble first) as four ASCII bytes.
+__device__ __forceinline__ uint32_t hex4(uint32_t t) {
+    const uint32_t z = __byte_perm(t, 0u, 0x4140);                 // [t.b0, 0, t.b1, 0]
+    const uint32_t nib = ((z << 4) | z) & 0x0F0F0F0Fu;             // [lo&15, lo>>4, hi&15, hi>>4]
+    const uint32_t x = __byte_perm(nib, 0u, 0x0123);               // [hi>>4, hi&15, lo>>4, lo&15]
+    return x + 0x30303030u + (((x + 0x06060606u) >> 4) & 0x01010101u) * 0x27u;  // 0-9 -> '0'.., 10-15 -> 'a'..
+}
+
+// Formats children [c0, c1) of the level at (cur_hash, cur_size) into msg (>= 208 words); returns
+// the message length in bytes, zero-pads the last 64-byte block, and accumulates the sizes.
+__device__ __forceinline__ uint32_t format_node(const uint8_t* __restrict__ cur_hash,
+                                                const uint64_t* __restrict__ cur_size, uint64_t first_child,
+                                                uint32_t n_children, uint32_t* msg, uint64_t* total_out) {
+    Packer pk{msg, 0u, 0ull, 0u};
+    uint64_t total = 0;
+    for (uint32_t c = 0; c < n_children; c++) {
+        const uint4* hp = reinterpret_cast<const uint4*>(cur_hash + (first_child + c) * 32);
+        const uint4 h0 = hp[0], h1 = hp[1];
+        const uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+        for (int wd = 0; wd < 4; wd++) {  // LE u64 word = (hw[2wd+1] << 32) | hw[2wd], printed high byte first
+            pk.put(hex4(hw[2 * wd + 1] >> 16), 4);
+            pk.put(hex4(hw[2 * wd + 1] & 0xFFFFu), 4);
+            pk.put(hex4(hw[2 * wd] >> 16), 4);
+            pk.put(hex4(hw[2 * wd] & 0xFFFFu), 4);
+        }
+        pk.put(0x203A20u, 3);  // " : "
+        const uint64_t sz = cur_size[first_child + c];
+        total += sz;
+        // decimal, most significant digit first; 32-bit arithmetic whenever the size allows
+        char dec[20];
+        int nd = 0;
+        if (sz >> 32) {
+            uint64_t t = sz;
+            do {
+                dec[nd++] = (char)('0' + (uint32_t)(t % 10u));
+                t /= 10u;
+            } while (t);
+        } else {
+            uint32_t t = (uint32_t)sz;
+            do {
+                dec[nd++] = (char)('0' + t % 10u);
+                t /= 10u;
+            } while (t);
+        }
+        while (nd) pk.put((uint32_t)dec[--nd], 1);
+        pk.put('\n', 1);
+    }
+    const uint32_t len = pk.bytes();
+    if (pk.pend) msg[pk.n++] = (uint32_t)pk.acc;
+    while (pk.n & 15u) msg[pk.n++] = 0u;  // zero padding of the final block
+    *total_out = total;
+    return len;
+}
+
+// Single-leaf keyed BLAKE3 (INTERNAL_NODE_KEY) of a formatted message.
+__device__ __forceinline__ void hash_node_message(const uint32_t* msg, uint32_t len, uint32_t (&cv)[8]) {
+    const uint32_t key[8] = XG_NODE_KEY_WORDS;
+#pragma unroll
+    for (int i = 0; i < 8; i++) cv[i] = key[i];
+    const uint32_t nb = len <= 64 ? 1u : (len + 63u) / 64u;
+    for (uint32_t b = 0; b < nb; b++) {
+        uint32_t m[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) m[i] = msg[b * 16 + i];
+        uint32_t flags = B3_KEYED_HASH;
+        if (b == 0) flags |= B3_CHUNK_START;
+        uint32_t bl = 64;
+        if (b == nb - 1) {
+            flags |= B3_CHUNK_END | B3_ROOT;
+            bl = len - b * 64;
+        }
+        b3_compress(cv, m, 0u, 0u, bl, flags);
+    }
+}
 
 __global__ void merkle_hash_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
                                    const uint8_t* __restrict__ cur_hash, const uint64_t* __restrict__ cur_size,
@@ -166,59 +254,108 @@ __global__ void merkle_hash_kernel(const uint64_t* __restrict__ slot_off, uint32
     const uint32_t gi = (uint32_t)(s - base);
     if (gi >= next_count[f]) return;
     const uint32_t c0 = group_start[base + gi], c1 = group_start[base + gi + 1];
-
-    MsgBuf msg;
-#pragma unroll 1
-    for (int i = 0; i < 208; i++) msg.w[i] = 0u;
-    msg.len = 0;
-    uint64_t total = 0;
-    for (uint32_t c = c0; c < c1; c++) {
-        const uint8_t* h = cur_hash + (base + c) * 32;
-        // MerkleHash::hex: four LE u64 words, each printed as 16 hex digits
-        for (int wd = 0; wd < 4; wd++)
-            for (int b = 7; b >= 0; b--) {
-                const uint32_t v = h[8 * wd + b];
-                msg.put(hex_digit(v >> 4));
-                msg.put(hex_digit(v & 15u));
-            }
-        msg.put(' ');
-        msg.put(':');
-        msg.put(' ');
-        const uint64_t sz = cur_size[base + c];
-        total += sz;
-        char dec[20];
-        int nd = 0;
-        uint64_t t = sz;
-        do {
-            dec[nd++] = (char)('0' + (t % 10));
-            t /= 10;
-        } while (t);
-        while (nd) msg.put((uint32_t)dec[--nd]);
-        msg.put('\n');
-    }
-    // single-leaf keyed BLAKE3 of the message
-    const uint32_t key[8] = XG_NODE_KEY_WORDS;
+    uint32_t msg[224];
+    uint64_t total;
+    const uint32_t len = format_node(cur_hash, cur_size, base + c0, c1 - c0, msg, &total);
     uint32_t cv[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) cv[i] = key[i];
-    const uint32_t nb = msg.len <= 64 ? 1u : (msg.len + 63u) / 64u;
-    for (uint32_t b = 0; b < nb; b++) {
-        uint32_t m[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++) m[i] = msg.w[b * 16 + i];
-        uint32_t flags = B3_KEYED_HASH;
-        if (b == 0) flags |= B3_CHUNK_START;
-        uint32_t bl = 64;
-        if (b == nb - 1) {
-            flags |= B3_CHUNK_END | B3_ROOT;
-            bl = msg.len - b * 64;
-        }
-        b3_compress(cv, m, 0u, 0u, bl, flags);
-    }
+    hash_node_message(msg, len, cv);
     uint4* dst = reinterpret_cast<uint4*>(next_hash + s * 32);
     dst[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
     dst[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
     next_size[s] = total;
+}
+
+// ---- last levels in one launch ------------------------------------------------------------------
+// Once every file's level is known to hold at most kFinishNodes nodes, one CTA per file runs all
+// remaining levels by itself (same grouping tables, kept in shared memory), which removes four
+// launches per level from the latency-bound tail of the tree.
+constexpr uint32_t kFinishNodes = 8192;
+constexpr uint32_t kFinishThreads = 256;  // one 32-node block per thread
+static_assert(kFinishNodes == kFinishThreads * 32, "one block per thread");
+
+__global__ void __launch_bounds__(kFinishThreads)
+    merkle_finish_kernel(const uint64_t* __restrict__ slot_off, const uint32_t* __restrict__ level_count,
+                         uint8_t* hash_a, uint64_t* size_a, uint8_t* hash_b, uint64_t* size_b,
+                         uint8_t* __restrict__ file_root) {
+    __shared__ uint64_t s_bits[kFinishThreads], s_out[kFinishThreads], s_cnt[kFinishThreads];
+    __shared__ uint32_t s_entry[kFinishThreads], s_base[kFinishThreads];
+    __shared__ uint32_t s_start[kFinishNodes / 3 + 4];
+    __shared__ uint32_t s_ng;
+    const uint32_t f = blockIdx.x, tid = threadIdx.x;
+    uint32_t n = level_count[f];
+    if (n == 0 || n > kFinishNodes) return;  // empty / already latched / (never: host bound) too large
+    const uint64_t base = slot_off[f];
+    uint8_t* cur_hash = hash_a + base * 32;
+    uint64_t* cur_size = size_a + base;
+    uint8_t* nxt_hash = hash_b + base * 32;
+    uint64_t* nxt_size = size_b + base;
+    while (n > 1) {
+        const uint32_t nb = (n + 31) / 32;
+        if (tid < nb) {  // A: block table
+            const uint32_t first = tid * 32;
+            uint64_t bits = 0;
+            for (uint32_t i = 0; i < 40 && first + i < n; i++)
+                bits |= (uint64_t)((cur_hash[(uint64_t)(first + i) * 32 + 24] & 3u) == 0u) << i;
+            uint64_t mo = 0, mc = 0;
+            for (uint32_t o = 0; o < 9; o++) {
+                uint32_t r = o, cnt = 0;
+                while (r < 32 && first + r < n) {
+                    r += group_len(bits, r, n - (first + r));
+                    cnt++;
+                }
+                mo |= (uint64_t)(r >= 32 ? r - 32 : 0) << (4 * o);
+                mc |= (uint64_t)cnt << (5 * o);
+            }
+            s_bits[tid] = bits;
+            s_out[tid] = mo;
+            s_cnt[tid] = mc;
+        }
+        __syncthreads();
+        if (tid == 0) {  // B: compose
+            uint32_t o = 0, total = 0;
+            for (uint32_t b = 0; b < nb; b++) {
+                s_entry[b] = o;
+                s_base[b] = total;
+                total += (uint32_t)(s_cnt[b] >> (5 * o)) & 31u;
+                o = (uint32_t)(s_out[b] >> (4 * o)) & 15u;
+            }
+            s_start[total] = n;
+            s_ng = total;
+        }
+        __syncthreads();
+        if (tid < nb) {  // C: emit group starts
+            const uint32_t first = tid * 32;
+            const uint64_t bits = s_bits[tid];
+            uint32_t r = s_entry[tid], w = s_base[tid];
+            while (r < 32 && first + r < n) {
+                s_start[w++] = first + r;
+                r += group_len(bits, r, n - (first + r));
+            }
+        }
+        __syncthreads();
+        const uint32_t ng = s_ng;
+        for (uint32_t g = tid; g < ng; g += kFinishThreads) {  // D: hash the new nodes
+            uint32_t msg[224];
+            uint64_t total;
+            const uint32_t c0 = s_start[g], c1 = s_start[g + 1];
+            const uint32_t len = format_node(cur_hash, cur_size, c0, c1 - c0, msg, &total);
+            uint32_t cv[8];
+            hash_node_message(msg, len, cv);
+            uint4* dst = reinterpret_cast<uint4*>(nxt_hash + (uint64_t)g * 32);
+            dst[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
+            dst[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
+            nxt_size[g] = total;
+        }
+        __syncthreads();
+        uint8_t* th = cur_hash;
+        cur_hash = nxt_hash;
+        nxt_hash = th;
+        uint64_t* ts = cur_size;
+        cur_size = nxt_size;
+        nxt_size = ts;
+        n = ng;
+    }
+    if (tid < 2) reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32)[tid] = reinterpret_cast<const uint4*>(cur_hash)[tid];
 }
 
 // Level-0 node sizes are the chunk lengths.
@@ -258,26 +395,27 @@ int launch_merkle(const PipelineBuffers& b, cudaStream_t st) {
         n++;
     }
     cudaMemcpyAsync(b.level_count[0], b.file_count, sizeof(uint32_t) * b.n_files, cudaMemcpyDeviceToDevice, st);
+    // Global level rounds while some file may still hold more than kFinishNodes nodes (host-side bound:
+    // a level of m nodes yields at most (m + 2) / 3), then one CTA per file finishes the tree.
     int cur = 0;
-    for (uint32_t level = 0; level <= b.max_levels; level++) {
-        if (b.n_slots) {
-            merkle_block_map_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
-                                                             b.level_count[cur], b.mk_bits, b.mk_out, b.mk_cnt);
-            n++;
-        }
+    for (uint64_t ub = b.max_nodes; ub > kFinishNodes && b.n_slots; ub = (ub + 2) / 3) {
+        merkle_block_map_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
+                                                         b.level_count[cur], b.mk_bits, b.mk_out, b.mk_cnt);
         merkle_compose_kernel<<<fblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
                                                        b.mk_out, b.mk_cnt, b.mk_entry, b.mk_base,
                                                        b.level_count[cur ^ 1], b.group_start, b.file_root);
-        n++;
-        if (level == b.max_levels || b.n_slots == 0) break;
         merkle_emit_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.level_count[cur], b.mk_bits,
                                                     b.mk_entry, b.mk_base, b.group_start);
         merkle_hash_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
                                                     b.node_size[cur], b.level_count[cur ^ 1], b.group_start,
                                                     b.node_hash[cur ^ 1], b.node_size[cur ^ 1]);
-        n += 2;
+        n += 4;
         cur ^= 1;
     }
+    merkle_finish_kernel<<<b.n_files, kFinishThreads, 0, st>>>(b.slot_off, b.level_count[cur], b.node_hash[cur],
+                                                              b.node_size[cur], b.node_hash[cur ^ 1],
+                                                              b.node_size[cur ^ 1], b.file_root);
+    n++;
     file_hash_kernel<<<fblocks, 128, 0, st>>>(b.n_files, b.file_count, b.file_root, b.file_hash);
     return n + 1;
 }

@@ -89,7 +89,7 @@ struct PipelineBuffers {
     // scan scratch
     uint64_t* scan_partial;     // [scan_blocks_cap]
     uint64_t* scalars;          // [8] device scalars: 0 = n_cand, 1 = n_groups, 2 = n_chunks
-    uint32_t max_levels;        // host bound on merkle depth
+    uint64_t max_nodes;         // host bound on the largest per-file chunk count (merkle level-0 size)
     uint32_t sm_count;          // SMs of the device (persistent-kernel grid size)
     // optional timing events (nullptr = off): [0,1] around gear_scan_kernel, [2,3] around leaf_group_kernel
     cudaEvent_t ev_kernel[4];
