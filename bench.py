@@ -87,7 +87,7 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.idx)],
+                                          "-lms", "20", "-i", str(self.idx)],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -215,7 +215,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scale", type=float, default=float(os.environ.get("XETBENCH_SCALE", "1.0")),
@@ -275,6 +275,9 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+        time.sleep(0.5)  # let nvidia-smi come up so that its samples fall inside the timed region
+        for _ in range(2):
+            step_device()  # keep the clocks at their loaded level while it does
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage = {k: 0.0 for k in ("gear_ms", "resolve_ms", "blake3_ms", "merkle_ms", "gear_kernel_ms", "leaf_kernel_ms")}
     launches = 0

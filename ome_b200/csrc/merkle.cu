@@ -23,7 +23,7 @@ namespace xetgpu {
 // (0..8) at which it enters the block.  Per level:
 //   A  one thread per 32-node block tabulates, for each of the 9 possible entry offsets, the exit
 //      offset and the number of group starts inside the block                    (parallel)
-//   B  one thread per file composes the block tables left to right: a shift and a mask per block
+//   B  one warp per file composes the block tables left to right: a shift and a mask per block
 //   C  one thread per block replays its 32 nodes from its now-known entry offset and writes the
 //      group starts                                                             (parallel)
 // Level bookkeeping for file f lives in the file's slot range [slot_off[f], slot_off[f+1]).
@@ -79,38 +79,55 @@ __global__ void merkle_block_map_kernel(const uint64_t* __restrict__ slot_off, u
     map_cnt[s] = mc;
 }
 
+// One WARP per file: the block tables of 32 consecutive blocks are loaded coalesced, one per lane,
+// and the chain is then advanced through them with register shuffles only (no memory latency on
+// the sequential path); every lane runs the same uniform recurrence and keeps the state at which
+// the chain entered its own block.
 __global__ void merkle_compose_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files,
                                       const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
                                       const uint64_t* __restrict__ map_out, const uint64_t* __restrict__ map_cnt,
                                       uint32_t* __restrict__ block_entry, uint32_t* __restrict__ block_base,
                                       uint32_t* __restrict__ next_count, uint32_t* __restrict__ group_start,
                                       uint8_t* __restrict__ file_root) {
-    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (f >= n_files) return;
     const uint32_t n = cur_count[f];
     const uint64_t base = slot_off[f];
     if (n <= 1) {
-        if (n == 1) {  // finished: latch the root
-            const uint4* src = reinterpret_cast<const uint4*>(cur_hash + base * 32);
-            uint4* dst = reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32);
-            dst[0] = src[0];
-            dst[1] = src[1];
-        }
-        next_count[f] = 0;
+        if (n == 1 && lane < 2)  // finished: latch the root
+            reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32)[lane] =
+                reinterpret_cast<const uint4*>(cur_hash + base * 32)[lane];
+        if (lane == 0) next_count[f] = 0;
         return;
     }
     const uint32_t nb = (n + 31) / 32;
     uint32_t o = 0, total = 0;
-#pragma unroll 8
-    for (uint32_t b = 0; b < nb; b++) {
-        const uint64_t mo = map_out[base + b], mc = map_cnt[base + b];
-        block_entry[base + b] = o;
-        block_base[base + b] = total;
-        total += (uint32_t)(mc >> (5 * o)) & 31u;
-        o = (uint32_t)(mo >> (4 * o)) & 15u;
+    for (uint32_t b0 = 0; b0 < nb; b0 += 32) {
+        const uint32_t mine = b0 + lane;
+        const uint64_t my_out = mine < nb ? map_out[base + mine] : 0ull;
+        const uint64_t my_cnt = mine < nb ? map_cnt[base + mine] : 0ull;
+        uint32_t my_entry = 0, my_base = 0;
+        const uint32_t m = nb - b0 < 32 ? nb - b0 : 32;
+        for (uint32_t k = 0; k < m; k++) {
+            const uint64_t mo = __shfl_sync(0xffffffffu, my_out, k);
+            const uint64_t mc = __shfl_sync(0xffffffffu, my_cnt, k);
+            if (lane == k) {
+                my_entry = o;
+                my_base = total;
+            }
+            total += (uint32_t)(mc >> (5 * o)) & 31u;
+            o = (uint32_t)(mo >> (4 * o)) & 15u;
+        }
+        if (mine < nb) {
+            block_entry[base + mine] = my_entry;
+            block_base[base + mine] = my_base;
+        }
     }
-    group_start[base + total] = n;  // sentinel; total <= (n + 2) / 3 < n for n >= 2
-    next_count[f] = total;
+    if (lane == 0) {
+        group_start[base + total] = n;  // sentinel; total <= (n + 2) / 3 < n for n >= 2
+        next_count[f] = total;
+    }
 }
 
 __global__ void merkle_emit_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
@@ -401,7 +418,7 @@ int launch_merkle(const PipelineBuffers& b, cudaStream_t st) {
     for (uint64_t ub = b.max_nodes; ub > kFinishNodes && b.n_slots; ub = (ub + 2) / 3) {
         merkle_block_map_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
                                                          b.level_count[cur], b.mk_bits, b.mk_out, b.mk_cnt);
-        merkle_compose_kernel<<<fblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
+        merkle_compose_kernel<<<(b.n_files * 32 + 127) / 128, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
                                                        b.mk_out, b.mk_cnt, b.mk_entry, b.mk_base,
                                                        b.level_count[cur ^ 1], b.group_start, b.file_root);
         merkle_emit_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.level_count[cur], b.mk_bits,

@@ -1,0 +1,237 @@
+"""Multi-GPU host logic: one process per GPU, `torch.distributed` for the (tiny) exchanges.
+
+The path shards in two ways:
+
+* by file  — every rank hashes whole files; nothing is exchanged but the per-file results
+  (BASELINE config 3).  `FilePartition` + `hash_files_partitioned`.
+* by byte range within one file — rank r owns bytes [begin_r, end_r) (BASELINE config 4).
+  Chunk boundaries are a carry chain across ranges, so `hash_file_by_ranges` speculates:
+    1. neighbours exchange the `RANGE_LEAD` bytes in front of each range (the 64-byte gear halo
+       plus one maximum chunk, so that the chunk straddling the range start can be hashed by
+       the rank that owns its end);
+    2. every rank hashes its whole range at once, pretending a cut sits exactly at its range
+       begin (rank 0 needs no pretence);
+    3. the true carry (8 bytes: the last cut at or before the range begin) then travels down the
+       ranks; a rank re-hashes only a small window at the front of its range from the true
+       carry and splices it onto its speculative chunk list at the first common cut — from a
+       shared cut on, the two chains are identical.  If the window holds no common cut it is
+       widened, in the worst case to the whole range (still exact);
+    4. rank 0 receives every rank's (hash, size) list and computes the merkle root / file hash.
+  The bulk work (2) runs on all ranks in parallel; the chain (3) costs a few small launches per hop.
+
+The engine is whatever object offers `hash_range`, `merkle_from_chunks` and `hash_buffers` with
+the signatures of `ome_b200.XetHasher` — the product passes a XetHasher (CUDA, no CPU fallback);
+the CPU tests drive the same code over gloo with an oracle-backed engine of their own.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+MAX_CHUNK = 131072
+RANGE_LEAD = MAX_CHUNK + 64
+FIX_WINDOW = 4 << 20   # first re-hash window after the true carry arrives
+
+
+# --------------------------------------------------------------------------------- partitioning
+@dataclass
+class FilePartition:
+    assignment: List[List[int]]     # per rank: file indices, in processing order
+    loads: List[int]                # per rank: bytes
+
+    @staticmethod
+    def lpt(sizes: Sequence[int], world: int) -> "FilePartition":
+        """Longest-processing-time-first: biggest file to the currently lightest rank."""
+        assignment = [[] for _ in range(world)]
+        loads = [0] * world
+        for i in sorted(range(len(sizes)), key=lambda i: (-sizes[i], i)):
+            r = min(range(world), key=lambda r: (loads[r], r))
+            assignment[r].append(i)
+            loads[r] += sizes[i]
+        return FilePartition(assignment, loads)
+
+
+def split_byte_ranges(file_len: int, world: int, align: int = 4096) -> List[Tuple[int, int]]:
+    """`world` contiguous ranges covering [0, file_len); interior bounds aligned down to `align`.
+    Every range except possibly the last is at least RANGE_LEAD long when the file allows it;
+    trailing ranks get empty ranges for very small files."""
+    if world <= 0:
+        raise ValueError("world must be positive")
+    per = max(-(-file_len // world), RANGE_LEAD + align)
+    bounds = [0]
+    for r in range(1, world):
+        b = min(file_len, (r * per) // align * align)
+        if file_len - b < RANGE_LEAD:      # do not leave a sliver for the last ranks: fold it into this one
+            b = file_len
+        bounds.append(max(b, bounds[-1]))
+    bounds.append(file_len)
+    return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
+# ------------------------------------------------------------------------------- file partition
+def hash_files_partitioned(engine, local_files: Sequence[Tuple[int, object]], n_files: int,
+                           group=None, comm_device: Optional[torch.device] = None):
+    """Every rank hashes its own files [(global index, bytes-like)], then all ranks receive all
+    results.  Returns (file_hashes uint8 [n_files, 32], n_chunks int64 [n_files])."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    dev = comm_device or torch.device("cpu")
+    hashes = torch.zeros(n_files, 32, dtype=torch.uint8)
+    counts = torch.zeros(n_files, dtype=torch.int64)
+    for idx, data in local_files:
+        n = _nbytes(data)
+        cl = engine.hash_buffers(data, [0, n])
+        hashes[idx] = torch.frombuffer(bytearray(cl.files[0].file_hash), dtype=torch.uint8)
+        counts[idx] = cl.files[0].n_chunks
+    if world > 1:
+        # disjoint rows are non-zero on exactly one rank: a sum all-reduce is a gather
+        h = hashes.to(torch.int32).to(dev)
+        c = counts.to(dev)
+        dist.all_reduce(h, group=group)
+        dist.all_reduce(c, group=group)
+        hashes, counts = h.to("cpu").to(torch.uint8), c.to("cpu")
+    return hashes.numpy(), counts.numpy()
+
+
+def _nbytes(data) -> int:
+    if hasattr(data, "numel"):
+        return data.numel() * data.element_size()
+    return np.asarray(data).nbytes if not isinstance(data, (bytes, bytearray, memoryview)) else len(data)
+
+
+# --------------------------------------------------------------------------------- byte ranges
+@dataclass
+class RangeOutcome:
+    chunk_ends: np.ndarray       # file-relative exclusive ends of the chunks this rank owns
+    chunk_hashes: np.ndarray     # [n, 32]
+    exit_cut: int
+    rehashed_bytes: int          # bytes of fix-up window(s) hashed after the true carry arrived
+    merkle_root: Optional[bytes] = None   # rank 0 only
+    file_hash: Optional[bytes] = None     # rank 0 only
+    n_chunks_total: Optional[int] = None  # rank 0 only
+
+
+def exchange_lead(piece: torch.Tensor, lead_capacity: int, ranges: Sequence[Tuple[int, int]], group=None) -> int:
+    """Halo exchange.  `piece` = [lead_capacity bytes of headroom][this rank's own range bytes]; the
+    call fills the last `lead` bytes of the headroom with the bytes that precede the range, received
+    from the previous rank, and sends this rank's last RANGE_LEAD bytes to the next one.  Ranges come
+    from split_byte_ranges: every non-empty range that has a non-empty successor is at least
+    RANGE_LEAD long, so one neighbour always holds the whole halo.  Returns lead."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    begin, end = ranges[rank]
+    n_own = end - begin
+    lead = min(begin, RANGE_LEAD) if n_own else 0
+    if lead > lead_capacity:
+        raise ValueError("headroom in front of the range is smaller than the halo")
+    ops = []
+    nxt = ranges[rank + 1] if rank + 1 < world else (0, 0)
+    if nxt[1] > nxt[0]:                                    # the next rank needs my tail
+        if n_own < RANGE_LEAD:
+            raise ValueError("a range followed by a non-empty range must be at least RANGE_LEAD bytes")
+        tail = piece[lead_capacity + n_own - RANGE_LEAD: lead_capacity + n_own].contiguous()
+        ops.append(dist.P2POp(dist.isend, tail, _peer(rank + 1, group), group))
+    buf = None
+    if lead:
+        buf = torch.empty(RANGE_LEAD, dtype=torch.uint8, device=piece.device)
+        ops.append(dist.P2POp(dist.irecv, buf, _peer(rank - 1, group), group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    if lead:
+        piece[lead_capacity - lead: lead_capacity] = buf[RANGE_LEAD - lead:]
+    return lead
+
+
+def _peer(r: int, group) -> int:
+    return dist.get_global_rank(group, r) if group is not None else r
+
+
+def _send_int(v: int, dst: int, device, group):
+    dist.send(torch.tensor([v], dtype=torch.int64, device=device), _peer(dst, group), group=group)
+
+
+def _recv_int(src: int, device, group) -> int:
+    t = torch.zeros(1, dtype=torch.int64, device=device)
+    dist.recv(t, _peer(src, group), group=group)
+    return int(t.item())
+
+
+def splice_at_common_cut(fix_ends, fix_hashes, spec_ends, spec_hashes):
+    """First cut of the re-synchronised chain that is also a cut of the speculative chain.  The chunk
+    that ENDS at that cut still starts at a different place in the two chains, so it is taken from
+    the re-synchronised one; everything after it is identical and comes from the speculative list.
+    Returns (ends, hashes) or None if the chains share no cut."""
+    common, fi, si = np.intersect1d(fix_ends, spec_ends, assume_unique=True, return_indices=True)
+    if common.size == 0:
+        return None
+    i, j = int(fi[0]), int(si[0])
+    return (np.concatenate([fix_ends[:i + 1], spec_ends[j + 1:]]),
+            np.concatenate([fix_hashes[:i + 1], spec_hashes[j + 1:]]))
+
+
+def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end: int, group=None,
+                        comm_device: Optional[torch.device] = None) -> RangeOutcome:
+    """`piece` holds bytes [begin - lead, end) of the file (tensor / array / buffer the engine accepts,
+    sliceable).  Collective over `group`: ranks must call it with consecutive ranges in rank order."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = comm_device or torch.device("cpu")
+    rehashed = 0
+    # 2. speculative pass over the whole range (rank 0's entry is the true one: the file start)
+    assumed = 0 if rank == 0 else begin
+    if end > begin or rank == 0:
+        spec = engine.hash_range(piece, file_len, begin, end, assumed)
+        ends, hashes, exit_cut = spec.chunk_ends, spec.chunk_hashes, spec.exit_cut
+    else:                                          # empty range: owns no chunk, only passes the carry on
+        ends, hashes, exit_cut = np.zeros(0, dtype=np.uint64), np.zeros((0, 32), dtype=np.uint8), assumed
+    # 3. carry chain
+    if rank > 0:
+        true_entry = _recv_int(rank - 1, dev, group)
+        if true_entry != assumed and end > begin:
+            window = FIX_WINDOW
+            while True:
+                w_end = min(end, begin + window)
+                fix = engine.hash_range(piece[: lead + (w_end - begin)], file_len, begin, w_end, true_entry)
+                rehashed += lead + (w_end - begin)
+                merged = splice_at_common_cut(fix.chunk_ends, fix.chunk_hashes, ends, hashes)
+                if merged is not None:
+                    ends, hashes = merged          # exit cut unchanged: the tail is the speculative chain
+                    break
+                if w_end == end:                   # chains never met inside this range: the re-hash is the answer
+                    ends, hashes, exit_cut = fix.chunk_ends, fix.chunk_hashes, fix.exit_cut
+                    break
+                window *= 4
+        elif end == begin:
+            exit_cut = true_entry                  # empty range: pass the carry through
+    if rank + 1 < world:
+        _send_int(int(exit_cut), rank + 1, dev, group)
+    out = RangeOutcome(ends, hashes, int(exit_cut), rehashed)
+    # 4. chunk lists to rank 0
+    counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    counts[rank] = ends.size
+    dist.all_reduce(counts, group=group)
+    counts = counts.cpu().numpy()
+    mine_e = torch.from_numpy(np.ascontiguousarray(ends).astype(np.int64)).to(dev)
+    mine_h = torch.from_numpy(np.ascontiguousarray(hashes).reshape(-1).copy()).to(dev)
+    if rank == 0:
+        all_e, all_h = [ends.astype(np.uint64)], [hashes]
+        for r in range(1, world):
+            n = int(counts[r])
+            e = torch.zeros(n, dtype=torch.int64, device=dev)
+            h = torch.zeros(n * 32, dtype=torch.uint8, device=dev)
+            if n:
+                dist.recv(e, _peer(r, group), group=group)
+                dist.recv(h, _peer(r, group), group=group)
+            all_e.append(e.cpu().numpy().astype(np.uint64))
+            all_h.append(h.cpu().numpy().reshape(n, 32))
+        e = np.concatenate(all_e)
+        h = np.concatenate(all_h)
+        sizes = np.diff(np.concatenate([[0], e])).astype(np.uint64)
+        out.merkle_root, out.file_hash = engine.merkle_from_chunks(h, sizes)
+        out.n_chunks_total = int(e.size)
+    elif ends.size:
+        dist.send(mine_e, _peer(0, group), group=group)
+        dist.send(mine_h, _peer(0, group), group=group)
+    return out

@@ -1,0 +1,133 @@
+"""World-size-2 (and 3) gloo tests of the multi-GPU host logic, on CPU with the oracle engine."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import xet_inputs
+import xet_oracle
+from ome_b200 import sharded
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, fn, args, ret):
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    for p in (here, os.path.join(os.path.dirname(here), "oracle"), os.path.dirname(here)):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ret[rank] = fn(rank, world, *args)
+    finally:
+        dist.destroy_process_group()
+
+
+def run_ranks(world, fn, *args):
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, free_port(), fn, args, ret), nprocs=world, join=True)
+    return [ret[r] for r in range(world)]
+
+
+def test_lpt_partition_balances():
+    sizes = [4976, 4999, 4915, 1168, 300, 7000, 10, 0]
+    p = sharded.FilePartition.lpt(sizes, 3)
+    assert sorted(i for a in p.assignment for i in a) == list(range(len(sizes)))
+    assert max(p.loads) - min(p.loads) <= max(sizes)
+    assert p.loads == [sum(sizes[i] for i in a) for a in p.assignment]
+
+
+def test_split_byte_ranges_properties():
+    for n, w in [(0, 2), (5, 2), (300000, 2), (10 << 20, 3), ((64 << 20) + 7, 8), (131136, 2)]:
+        r = sharded.split_byte_ranges(n, w)
+        assert len(r) == w and r[0][0] == 0 and r[-1][1] == n
+        assert all(r[i][1] == r[i + 1][0] for i in range(w - 1))
+        for i in range(w - 1):
+            if r[i + 1][1] > r[i + 1][0]:          # non-empty successor => this range can feed its halo
+                assert r[i][1] - r[i][0] >= sharded.RANGE_LEAD
+
+
+def _file_partition(rank, world, sizes):
+    from oracle_engine import OracleEngine
+    part = sharded.FilePartition.lpt(sizes, world)
+    local = [(i, xet_inputs.splitmix_bytes(700 + i, sizes[i])) for i in part.assignment[rank]]
+    h, c = sharded.hash_files_partitioned(OracleEngine(), local, len(sizes))
+    return h.tobytes(), c.tolist()
+
+
+def test_file_partition_gloo_world2():
+    sizes = [300000, 0, 70000, 1 << 20, 5, 200000, 9000]
+    out = run_ranks(2, _file_partition, sizes)
+    assert out[0] == out[1]                                 # every rank ends with every result
+    hashes = np.frombuffer(out[0][0], dtype=np.uint8).reshape(-1, 32)
+    for i, n in enumerate(sizes):
+        ref = xet_oracle.hash_file(xet_inputs.splitmix_bytes(700 + i, n))
+        assert hashes[i].tobytes() == ref.file_hash
+        assert out[0][1][i] == ref.chunk_ends.size
+
+
+def _byte_ranges(rank, world, spec, use_exchange):
+    from oracle_engine import OracleEngine
+    data = xet_inputs.build(spec)
+    n = data.size
+    ranges = sharded.split_byte_ranges(n, world)
+    begin, end = ranges[rank]
+    cap = sharded.RANGE_LEAD
+    piece = torch.zeros(cap + (end - begin), dtype=torch.uint8)
+    piece[cap:] = torch.from_numpy(data[begin:end].copy())  # a rank loads only its own range ...
+    if use_exchange:
+        lead = sharded.exchange_lead(piece, cap, ranges)      # ... and receives the halo from its neighbour
+    else:
+        lead = min(begin, cap) if end > begin else 0
+        piece[cap - lead:cap] = torch.from_numpy(data[begin - lead:begin].copy())
+    assert bytes(piece[cap - lead:cap].numpy()) == bytes(data[begin - lead:begin])
+    eng = OracleEngine()
+    out = sharded.hash_file_by_ranges(eng, piece[cap - lead:], lead, n, begin, end)
+    return dict(root=out.merkle_root, fh=out.file_hash, n=out.n_chunks_total, ends=out.chunk_ends.tolist(),
+                rehashed=out.rehashed_bytes, calls=eng.range_calls, range=(begin, end))
+
+
+@pytest.mark.parametrize("world,spec", [
+    (2, [["splitmix", 81, (6 << 20) + 12345]]),
+    (3, [["splitmix", 82, 9 << 20]]),
+    # chains that cannot re-merge: no candidates after an unaligned prefix -> whole-range fallback
+    (2, [["splitmix", 83, (1 << 20) + 7], ["zeros", 7 << 20]]),
+    # tiny file: every rank but the first owns an empty range
+    (2, [["splitmix", 84, 50000]]),
+    (3, [["zeros", 0]]),
+], ids=["w2-random", "w3-random", "w2-zeros-nomerge", "w2-tiny", "w3-empty"])
+def test_byte_range_partition_gloo(world, spec):
+    data = xet_inputs.build(spec)
+    ref = xet_oracle.hash_file(data)
+    out = run_ranks(world, _byte_ranges, spec, True)
+    assert out[0]["fh"] == ref.file_hash
+    assert out[0]["n"] == ref.chunk_ends.size
+    if ref.chunk_ends.size:
+        assert out[0]["root"] == ref.merkle_root
+    assert all(o["fh"] is None for o in out[1:])            # the combine runs on rank 0 only
+    ends = [e for o in out for e in o["ends"]]
+    assert ends == [int(x) for x in ref.chunk_ends]
+    for o in out:                                           # each rank owns exactly the chunks ending in its range
+        assert all(o["range"][0] < e <= o["range"][1] for e in o["ends"])
+
+
+def test_fixup_window_is_small_on_random_data():
+    """After the true carry arrives a rank re-hashes one small window, not its range."""
+    spec = [["splitmix", 85, 24 << 20]]
+    out = run_ranks(2, _byte_ranges, spec, False)
+    begin, end = out[1]["range"]
+    assert 0 < out[1]["rehashed"] <= sharded.FIX_WINDOW + sharded.RANGE_LEAD < end - begin
+    assert len(out[1]["calls"]) == 2                        # speculative pass + one fix-up window
