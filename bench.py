@@ -276,8 +276,8 @@ def main():
     if rank == 0:
         sampler.start()
         time.sleep(0.5)  # let nvidia-smi come up so that its samples fall inside the timed region
-        for _ in range(2):
-            step_device()  # keep the clocks at their loaded level while it does
+    for _ in range(2):
+        step_device()  # every rank (the step holds a collective): clocks back at their loaded level
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage = {k: 0.0 for k in ("gear_ms", "resolve_ms", "blake3_ms", "merkle_ms", "gear_kernel_ms", "leaf_kernel_ms")}
     launches = 0
