@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libxetgpu.so")
+LIB_PATH = os.environ.get("XETGPU_LIBRARY") or os.path.join(_HERE, "libxetgpu.so")
 
 
 class XetError(C.Structure):  # pkg/xet/xet.h:86-90

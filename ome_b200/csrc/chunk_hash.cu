@@ -28,6 +28,21 @@ namespace xetgpu {
 int launch_chunk_bookkeeping(const PipelineBuffers& b, cudaStream_t st);  // resolve.cu
 
 
+// The subtree merges are 3 compressions per 64 leaf compressions; keeping them out of line keeps one
+// copy of the ~13 KB compression body in the leaf kernel's instruction stream.
+__device__ __noinline__ void parent_out_of_line(const uint32_t* l, const uint32_t* r, uint32_t root, uint32_t* out) {
+    const uint32_t key[8] = XG_DATA_KEY_WORDS;
+    uint32_t lv[8], rv[8], o[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        lv[i] = l[i];
+        rv[i] = r[i];
+    }
+    b3_parent(key, lv, rv, root != 0u, o);
+#pragma unroll
+    for (int i = 0; i < 8; i++) out[i] = o[i];
+}
+
 constexpr int kLeafThreads = kLeafWarpsPerCta * 32;
 constexpr int kLeafStage = 32 * kLeafRow;                       // bytes of shared memory per warp
 constexpr int kLeafSmem = kLeafWarpsPerCta * kLeafStage;
@@ -121,7 +136,7 @@ __global__ void __launch_bounds__(kLeafThreads)
 #pragma unroll
         for (int i = 0; i < 8; i++) cv[i] = key[i];
 #pragma unroll 1
-        for (uint32_t half = 0; half < 1024u / kLeafHalfBytes; half++) {
+        for (uint32_t half = 0; half < (1024u + kLeafHalfBytes - 1u) / kLeafHalfBytes; half++) {
             // stage this half leaf of all 32 lanes: one bulk copy per lane, one mbarrier phase
             const uint32_t hbeg = half * kLeafHalfBytes;
             const bool hact = active && (hbeg < llen || half == 0);
@@ -146,27 +161,18 @@ __global__ void __launch_bounds__(kLeafThreads)
 #pragma unroll
                 for (int i = 0; i < 8; i++) a[i] = cv[i];
             } else if (li == 1) {
-                uint32_t l[8];
-#pragma unroll
-                for (int i = 0; i < 8; i++) l[i] = a[i];
-                b3_parent(key, l, cv, /*root=*/cleaves == 2u, a);
+                parent_out_of_line(a, cv, cleaves == 2u, a);
             } else if (li == 2) {
 #pragma unroll
                 for (int i = 0; i < 8; i++) bq[i] = cv[i];
             } else {
-                uint32_t l[8];
-#pragma unroll
-                for (int i = 0; i < 8; i++) l[i] = bq[i];
-                b3_parent(key, l, cv, false, bq);
+                parent_out_of_line(bq, cv, 0u, bq);
             }
         }
     }
     if (!valid) return;
     if (gleaves >= 3) {
-        uint32_t l[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) l[i] = a[i];
-        b3_parent(key, l, bq, /*root=*/cleaves <= (uint32_t)kLeavesPerGroup, a);
+        parent_out_of_line(a, bq, cleaves <= (uint32_t)kLeavesPerGroup, a);
     }
     uint4* dst = cleaves <= (uint32_t)kLeavesPerGroup ? reinterpret_cast<uint4*>(chunk_hash + (uint64_t)slot * 32)
                                                        : reinterpret_cast<uint4*>(group_cv + g * 8);

@@ -71,9 +71,15 @@ int launch_fill_splitmix(uint8_t* dst, uint64_t seed, uint64_t byte_off, uint64_
 // the rolling hash: 64 / 4096 = 1.6 % overhead.
 constexpr int kGearRow = 4096;
 static_assert(kGearTile == 32 * kGearRow, "a tile is 32 rows");
-constexpr int kGearWarps = 8;
+#ifndef XG_GEAR_WARPS
+#define XG_GEAR_WARPS 16
+#endif
+#ifndef XG_GEAR_STAGES
+#define XG_GEAR_STAGES 2
+#endif
+constexpr int kGearWarps = XG_GEAR_WARPS;
 constexpr int kGearThreads = kGearWarps * 32;
-constexpr int kGearStages = 4;
+constexpr int kGearStages = XG_GEAR_STAGES;
 constexpr int kGearBox = 32 * 128;                                           // bytes per box
 constexpr int kGearBoxesPerTile = 1 + kGearRow / 128;                        // halo box + 32
 constexpr int kGearTableBytes = 256 * 32 * 8;                                // [byte][lane] u64, 64 KiB

@@ -24,10 +24,16 @@ constexpr uint32_t kSegCap = (uint32_t)(kSegBytes / kMinChunk) + 2;
 // ---- K3 geometry.  A "group" is up to kLeavesPerGroup consecutive 1 KiB BLAKE3 leaves of one
 // chunk, hashed by one lane, which also merges them into one subtree chaining value.
 constexpr int kLeavesPerGroup = 4;
-constexpr int kLeafHalfBytes = 512;                     // bytes of a leaf staged per round
+#ifndef XG_LEAF_PART
+#define XG_LEAF_PART 512
+#endif
+#ifndef XG_LEAF_WARPS
+#define XG_LEAF_WARPS 4
+#endif
+constexpr int kLeafHalfBytes = XG_LEAF_PART;            // bytes of a leaf staged per round
 constexpr int kLeafHalfBlocks = kLeafHalfBytes / 64;
 constexpr int kLeafRow = kLeafHalfBytes + 16;           // smem bytes per staged half leaf (+16: alignment slack)
-constexpr int kLeafWarpsPerCta = 4;                     // 66 KiB per CTA, 3 CTAs = 12 warps per SM
+constexpr int kLeafWarpsPerCta = XG_LEAF_WARPS;          // 4 x 16.5 KiB = 66 KiB per CTA, 3 CTAs = 12 warps per SM
 
 struct PipelineBuffers {
     // inputs
