@@ -296,3 +296,31 @@ def test_full_size_shard_properties(hasher):
     pref = xet_oracle.hash_file(xet_inputs.splitmix_bytes(1, 64 << 20))
     assert np.array_equal(ends[:k], pref.chunk_ends[:k])
     assert np.array_equal(hashes[:k], pref.chunk_hashes[:k])
+
+
+def test_xetsum_cli_cpp_consumer(tmp_path):
+    """tools/xetsum: a plain C++ program over the C ABI (the role of OME's cgo wrappers)."""
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "tools", "xetsum")
+    if not os.path.exists(exe):
+        pytest.skip("tools/xetsum not built")
+    cases = {c["name"]: c for c in SMALL}
+    names = ["hello_world", "empty", "zeros_131073", "splitmix_seed1_1MiB"]
+    paths = []
+    for n in names:
+        p = tmp_path / (n + ".bin")
+        xet_inputs.build(cases[n]["spec"]).tofile(p)
+        paths.append(str(p))
+    out = subprocess.run([exe] + paths, capture_output=True, text=True, check=True).stdout.splitlines()
+    assert [l.split("  ")[0] for l in out] == [cases[n]["file_hash"] for n in names]
+    listing = tmp_path / "sums.txt"
+    listing.write_text("\n".join(out) + "\n")
+    ok = subprocess.run([exe, "-c", str(listing)], capture_output=True, text=True)
+    assert ok.returncode == 0 and ok.stdout.count(": OK") == len(names)
+    listing.write_text("0" * 64 + "  " + paths[0] + "\n")
+    bad = subprocess.run([exe, "-c", str(listing)], capture_output=True, text=True)
+    assert bad.returncode == 1 and "FAILED" in bad.stdout
+    ch = subprocess.run([exe, "--chunks", paths[3]], capture_output=True, text=True, check=True).stdout.splitlines()
+    assert len(ch) == 1 + cases["splitmix_seed1_1MiB"]["n_chunks"]
+    assert ch[1].split() == ["25125", cases["splitmix_seed1_1MiB"]["chunk_hashes"][0]]
