@@ -285,14 +285,24 @@ def main():
     ev0.record(stream)
     for _ in range(args.steps):
         cl = step_device()
-        t = hasher.last_timings()
-        for k in stage:
-            stage[k] += t[k]
-        launches += t["kernel_launches"]
+        launches += hasher.last_timings()["kernel_launches"]
         assert [f.file_hash for f in cl.files] == ref_hashes
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
+    # per-kernel durations for the roofline: the same step with the file groups run one after the other on one
+    # stream (in the timed loop above two groups overlap on two streams, which stretches each kernel's own time)
+    iso = ome_b200.XetHasher(device=local_rank, stream=stream.cuda_stream, stage_timing=True, overlap=False)
+    iso_steps = 3
+    for i in range(iso_steps + 1):
+        cl_iso = iso.hash_buffers(buf, off_np, memory=ome_b200.hasher.MEM_DEVICE)
+        if i:  # first call warms the workspace
+            t = iso.last_timings()
+            for k in stage:
+                stage[k] += t[k]
+    assert [f.file_hash for f in cl_iso.files] == ref_hashes
+    iso.close()
+    stage = {k: v * args.steps / iso_steps for k, v in stage.items()}  # reported per step below
     clocks = sampler.stop() if rank == 0 else None
     tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:

@@ -97,6 +97,7 @@ typedef struct {
 } XetGpuConfig;
 
 #define XETGPU_CTX_STAGE_TIMING 1u /* record CUDA events around every stage (xetgpu_last_timings) */
+#define XETGPU_CTX_NO_OVERLAP 2u   /* run file groups one after the other on one stream (per-kernel timing) */
 
 /* Where the bytes passed to xetgpu_hash_buffers live. */
 enum {

@@ -89,18 +89,25 @@ struct XetGpuContext {
     uint64_t staging_bytes = 64ull << 20;
     uint64_t max_batch_bytes = 8ull << 30;
     std::mutex mu;
-    // workspace (grow-only)
-    Arena ws;
+    // Two lanes: a lane is a stream with its own grow-only workspace, pinned metadata area and timing
+    // events.  Lane 0 runs on the context's stream; batches of several files alternate between the lanes
+    // so that one group's copies and gear pass overlap the previous group's hashing.
+    struct Lane {
+        cudaStream_t stream = nullptr;
+        Arena ws;
+        uint8_t* h_meta = nullptr;
+        uint64_t h_meta_cap = 0;
+        cudaEvent_t ev[8] = {};
+        cudaEvent_t ev_kernel[4] = {};
+    } lanes[2];
+    cudaEvent_t ev_fork = nullptr;
+    cudaEvent_t ev_gear_done[2] = {nullptr, nullptr};
+    uint64_t min_group_bytes = 256ull << 20;  // smallest file group worth its own lane (XETGPU_MIN_GROUP_BYTES)
     uint8_t* d_input = nullptr;  // device copy of host inputs
     uint64_t d_input_cap = 0;
     uint8_t* h_stage[2] = {nullptr, nullptr};  // pinned ingestion buffers
     cudaEvent_t stage_free[2] = {nullptr, nullptr};
-    uint8_t* h_meta = nullptr;  // pinned metadata / readback area
-    uint64_t h_meta_cap = 0;
     uint64_t cand_cap_hint = 0;
-    // timing
-    cudaEvent_t ev[8] = {};
-    cudaEvent_t ev_kernel[4] = {};
     XetGpuTimings last = {};
     // progress
     XetProgressCallback progress = nullptr;
@@ -109,14 +116,16 @@ struct XetGpuContext {
     std::chrono::steady_clock::time_point last_progress;
 };
 
-static XetError* ensure_meta(XetGpuContext* c, uint64_t bytes) {
-    if (bytes <= c->h_meta_cap) return nullptr;
-    if (c->h_meta) cudaFreeHost(c->h_meta);
-    c->h_meta = nullptr;
-    c->h_meta_cap = 0;
+typedef XetGpuContext::Lane Lane;
+
+static XetError* ensure_meta(Lane* l, uint64_t bytes) {
+    if (bytes <= l->h_meta_cap) return nullptr;
+    if (l->h_meta) cudaFreeHost(l->h_meta);
+    l->h_meta = nullptr;
+    l->h_meta_cap = 0;
     uint64_t cap = std::max<uint64_t>(bytes * 2, 1 << 20);
-    CU(cudaMallocHost((void**)&c->h_meta, cap));
-    c->h_meta_cap = cap;
+    CU(cudaMallocHost((void**)&l->h_meta, cap));
+    l->h_meta_cap = cap;
     return nullptr;
 }
 
@@ -164,8 +173,18 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
         }
         c->own_stream = true;
     }
-    for (auto& ev : c->ev) cudaEventCreate(&ev);
-    for (auto& ev : c->ev_kernel) cudaEventCreate(&ev);
+    c->lanes[0].stream = c->stream;
+    cudaStreamCreateWithFlags(&c->lanes[1].stream, cudaStreamNonBlocking);
+    for (auto& l : c->lanes) {
+        for (auto& ev : l.ev) cudaEventCreate(&ev);
+        for (auto& ev : l.ev_kernel) cudaEventCreate(&ev);
+    }
+    cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    for (auto& ev : c->ev_gear_done) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (const char* v = getenv("XETGPU_MIN_GROUP_BYTES")) {  // test knob: exercise the two-lane path on small inputs
+        unsigned long long n = strtoull(v, nullptr, 10);
+        if (n) c->min_group_bytes = n;
+    }
     for (auto& ev : c->stage_free) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
     init_gear_kernels();
     init_chunk_hash_kernels();
@@ -182,15 +201,22 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    if (c->ws.base) cudaFree(c->ws.base);
+    for (auto& l : c->lanes) {
+        if (l.stream) cudaStreamSynchronize(l.stream);
+        if (l.ws.base) cudaFree(l.ws.base);
+        if (l.h_meta) cudaFreeHost(l.h_meta);
+        for (auto& ev : l.ev)
+            if (ev) cudaEventDestroy(ev);
+        for (auto& ev : l.ev_kernel)
+            if (ev) cudaEventDestroy(ev);
+    }
+    if (c->lanes[1].stream) cudaStreamDestroy(c->lanes[1].stream);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    for (auto& ev : c->ev_gear_done)
+        if (ev) cudaEventDestroy(ev);
     if (c->d_input) cudaFree(c->d_input);
     for (auto& p : c->h_stage)
         if (p) cudaFreeHost(p);
-    if (c->h_meta) cudaFreeHost(c->h_meta);
-    for (auto& ev : c->ev)
-        if (ev) cudaEventDestroy(ev);
-    for (auto& ev : c->ev_kernel)
-        if (ev) cudaEventDestroy(ev);
     for (auto& ev : c->stage_free)
         if (ev) cudaEventDestroy(ev);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -299,8 +325,8 @@ static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, u
     return p;
 }
 
-static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool dry, uint64_t* need) {
-    Arena a = c->ws;
+static XetError* carve(Lane* l, const Plan& p, PipelineBuffers* b, bool dry, uint64_t* need) {
+    Arena a = l->ws;
     a.used = 0;
     if (dry) a.base = nullptr;
     const uint64_t F = p.n_files, S = p.n_slots, T = p.n_tiles;
@@ -363,21 +389,21 @@ static XetError* carve(XetGpuContext* c, const Plan& p, PipelineBuffers* b, bool
     return nullptr;
 }
 
-static XetError* ensure_workspace(XetGpuContext* c, const Plan& p, PipelineBuffers* b) {
+static XetError* ensure_workspace(Lane* l, const Plan& p, PipelineBuffers* b) {
     uint64_t need = 0;
-    carve(c, p, b, true, &need);
-    if (need > c->ws.cap) {
-        if (c->ws.base) {
-            cudaStreamSynchronize(c->stream);
-            cudaFree(c->ws.base);
+    carve(l, p, b, true, &need);
+    if (need > l->ws.cap) {
+        if (l->ws.base) {
+            cudaStreamSynchronize(l->stream);
+            cudaFree(l->ws.base);
         }
-        c->ws.base = nullptr;
-        c->ws.cap = 0;
+        l->ws.base = nullptr;
+        l->ws.cap = 0;
         uint64_t cap = need + need / 8;
-        CU(cudaMalloc((void**)&c->ws.base, cap));
-        c->ws.cap = cap;
+        CU(cudaMalloc((void**)&l->ws.base, cap));
+        l->ws.cap = cap;
     }
-    return carve(c, p, b, false, &need);
+    return carve(l, p, b, false, &need);
 }
 
 // ---------------------------------------------------------------------------------- ingestion
@@ -399,12 +425,12 @@ static bool host_ptr_is_pinned(const void* p) {
     return attr.type == cudaMemoryTypeHost;
 }
 
-static XetError* ingest_host(XetGpuContext* c, const uint8_t* src, uint64_t bytes, uint8_t* d_dst) {
+static XetError* ingest_host(XetGpuContext* c, cudaStream_t stream, const uint8_t* src, uint64_t bytes, uint8_t* d_dst) {
     if (bytes == 0) return nullptr;
     if (host_ptr_is_pinned(src)) {
         for (uint64_t o = 0; o < bytes; o += c->staging_bytes) {
             uint64_t n = std::min<uint64_t>(c->staging_bytes, bytes - o);
-            CU(cudaMemcpyAsync(d_dst + o, src + o, n, cudaMemcpyHostToDevice, c->stream));
+            CU(cudaMemcpyAsync(d_dst + o, src + o, n, cudaMemcpyHostToDevice, stream));
         }
         return nullptr;
     }
@@ -414,8 +440,8 @@ static XetError* ingest_host(XetGpuContext* c, const uint8_t* src, uint64_t byte
         uint64_t n = std::min<uint64_t>(c->staging_bytes, bytes - o);
         CU(cudaEventSynchronize(c->stage_free[i]));  // the copy that last used this buffer has drained
         memcpy(c->h_stage[i], src + o, n);
-        CU(cudaMemcpyAsync(d_dst + o, c->h_stage[i], n, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaEventRecord(c->stage_free[i], c->stream));
+        CU(cudaMemcpyAsync(d_dst + o, c->h_stage[i], n, cudaMemcpyHostToDevice, stream));
+        CU(cudaEventRecord(c->stage_free[i], stream));
     }
     return nullptr;
 }
@@ -440,147 +466,356 @@ struct RunOptions {
     bool skip_merkle = false;
 };
 
+// One group of files in flight on a lane: everything launch_group enqueued and finish_group reads.
+struct GroupState {
+    Plan plan;
+    PipelineBuffers b{};
+    uint64_t total = 0;
+    size_t n_files = 0;
+    int launches = 0;
+    bool had_h2d = false;
+    // pinned readback area
+    uint64_t* h_scalars = nullptr;
+    uint64_t* h_base = nullptr;
+    uint32_t* h_count = nullptr;
+    uint8_t* h_hash = nullptr;
+    uint8_t* h_root = nullptr;
+};
+
+// Enqueue the whole pipeline for one group on `lane` (no host synchronisation).
 // d_data: device bytes; offsets: host, relative to d_data.
-static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uint64_t* offsets, size_t n_files,
-                              const RunOptions& opt, XetGpuResult** out_result) {
+static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_data, const uint64_t* offsets,
+                              size_t n_files, const RunOptions& opt, GroupState* g,
+                              cudaEvent_t gear_after = nullptr, cudaEvent_t gear_done = nullptr) {
     const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
     const uint64_t total = n_files ? offsets[n_files] : 0;
-    for (int attempt = 0; attempt < 3; attempt++) {
-        Plan plan = make_plan(offsets, n_files, total, c->cand_cap_hint);
-        PipelineBuffers b{};
-        if (XetError* e = ensure_workspace(c, plan, &b)) return e;
-        b.data = d_data;
-        if (timing)
-            for (int i = 0; i < 4; i++) b.ev_kernel[i] = c->ev_kernel[i];
-        // metadata upload through pinned memory
-        const uint64_t F = n_files;
-        const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
-        if (XetError* e = ensure_meta(c, meta_bytes)) return e;
-        uint64_t* h_off = reinterpret_cast<uint64_t*>(c->h_meta);
-        uint64_t* h_slot = h_off + (F + 1);
-        memcpy(h_off, offsets, (F + 1) * 8);
-        memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
-        uint64_t* h_seg = h_slot + (F + 1);
-        memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
-        cudaStream_t st = c->stream;
-        int launches = 0;
-        if (timing) cudaEventRecord(c->ev[0], st);
-        CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-        CU(cudaMemsetAsync(b.scalars, 0, 64, st));
-        b.sm_count = c->sm_count;
-        cudaError_t gear_err = cudaSuccess;
-        launches += launch_gear(b, st, &gear_err);
-        if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
-        if (timing) cudaEventRecord(c->ev[1], st);
-        launches += launch_resolve(b, opt.range, st);
-        if (timing) cudaEventRecord(c->ev[2], st);
-        if (!opt.resolve_only) {
-            launches += launch_chunk_hash(b, st);
-            launches += launch_gather(b, st);
-            if (timing) cudaEventRecord(c->ev[3], st);
-            if (!opt.skip_merkle) launches += launch_merkle(b, st);
-            if (timing) cudaEventRecord(c->ev[4], st);
-        } else {
-            launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
-                                        b.scalars + kScalarChunks, st);
-            if (timing) {
-                cudaEventRecord(c->ev[3], st);
-                cudaEventRecord(c->ev[4], st);
-            }
-        }
-        CU(cudaGetLastError());
-        // readback: scalars, per-file counts, bases, roots, hashes
-        uint8_t* h_rb = c->h_meta + (F + 1) * 24;
-        uint64_t* h_scalars = reinterpret_cast<uint64_t*>(h_rb);
-        uint64_t* h_base = h_scalars + 8;
-        uint32_t* h_count = reinterpret_cast<uint32_t*>(h_base + (F + 2));
-        uint8_t* h_hash = reinterpret_cast<uint8_t*>(h_count + (F + 1 + ((F + 1) & 1)));
-        uint8_t* h_root = h_hash + (F + 1) * 32;
-        CU(cudaMemcpyAsync(h_scalars, b.scalars, 64, cudaMemcpyDeviceToHost, st));
-        if (F) {
-            CU(cudaMemcpyAsync(h_base, b.file_chunk_base, (F + 1) * 8, cudaMemcpyDeviceToHost, st));
-            CU(cudaMemcpyAsync(h_count, b.file_count, F * 4, cudaMemcpyDeviceToHost, st));
-            if (!opt.resolve_only && !opt.skip_merkle) {
-                CU(cudaMemcpyAsync(h_hash, b.file_hash, F * 32, cudaMemcpyDeviceToHost, st));
-                CU(cudaMemcpyAsync(h_root, b.file_root, F * 32, cudaMemcpyDeviceToHost, st));
-            }
-        }
-        if (timing) cudaEventRecord(c->ev[5], st);
-        CU(cudaStreamSynchronize(st));
-        const uint64_t n_cand = h_scalars[kScalarCand];
-        if (n_cand > plan.cand_cap) {  // candidate list overflowed (dense data): grow and redo
-            c->cand_cap_hint = n_cand + n_cand / 8 + 1024;
-            continue;
-        }
-        const uint64_t n_chunks = F ? h_base[F] : 0;
-        if (opt.exit_cut_abs) {
-            uint64_t last = opt.range ? opt.range->walk_start : 0;
-            if (n_chunks) CU(cudaMemcpy(&last, b.slot_end + (plan.slot_off[F - 1] + h_count[F - 1] - 1), 8,
-                                        cudaMemcpyDeviceToHost));
-            *opt.exit_cut_abs = last;
-        }
-        XetGpuResult* r = nullptr;
-        if (out_result) {
-            r = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
-            if (!r) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
-            r->n_files = n_files;
-            r->files = (XetGpuFileResult*)calloc(n_files ? n_files : 1, sizeof(XetGpuFileResult));
-            for (size_t f = 0; f < n_files; f++) {
-                XetGpuFileResult& fr = r->files[f];
-                if (!opt.resolve_only && !opt.skip_merkle) {
-                    memcpy(fr.file_hash, h_hash + f * 32, 32);
-                    memcpy(fr.merkle_root, h_root + f * 32, 32);
-                }
-                fr.size = offsets[f + 1] - offsets[f];
-                fr.n_chunks = h_count[f];
-                fr.first_chunk = h_base[f];
-            }
-            if (opt.want_chunks && n_chunks) {
-                r->n_chunks = n_chunks;
-                r->chunk_ends = (uint64_t*)malloc(n_chunks * 8);
-                r->chunk_hashes = (uint8_t*)malloc(n_chunks * 32);
-                if (!r->chunk_ends || !r->chunk_hashes) {
-                    xetgpu_free_result(r);
-                    return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
-                }
-                if (opt.resolve_only) {
-                    // ends only: gather was skipped; single file in this mode
-                    CU(cudaMemcpyAsync(r->chunk_ends, b.slot_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
-                    memset(r->chunk_hashes, 0, n_chunks * 32);
-                } else {
-                    CU(cudaMemcpyAsync(r->chunk_ends, b.out_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
-                    CU(cudaMemcpyAsync(r->chunk_hashes, b.out_hash, n_chunks * 32, cudaMemcpyDeviceToHost, st));
-                }
-                CU(cudaStreamSynchronize(st));
-                if (opt.end_bias)
-                    for (uint64_t i = 0; i < n_chunks; i++) r->chunk_ends[i] += opt.end_bias;
-            }
-            *out_result = r;
-        }
+    g->total = total;
+    g->n_files = n_files;
+    g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint);
+    const Plan& plan = g->plan;
+    PipelineBuffers& b = g->b;
+    b = PipelineBuffers{};
+    if (XetError* e = ensure_workspace(lane, plan, &b)) return e;
+    b.data = d_data;
+    if (timing)
+        for (int i = 0; i < 4; i++) b.ev_kernel[i] = lane->ev_kernel[i];
+    // metadata upload through pinned memory
+    const uint64_t F = n_files;
+    const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
+    if (XetError* e = ensure_meta(lane, meta_bytes)) return e;
+    uint64_t* h_off = reinterpret_cast<uint64_t*>(lane->h_meta);
+    uint64_t* h_slot = h_off + (F + 1);
+    uint64_t* h_seg = h_slot + (F + 1);
+    memcpy(h_off, offsets, (F + 1) * 8);
+    memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
+    memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
+    cudaStream_t st = lane->stream;
+    int launches = 0;
+    if (timing) cudaEventRecord(lane->ev[0], st);
+    CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(b.scalars, 0, 64, st));
+    b.sm_count = c->sm_count;
+    cudaError_t gear_err = cudaSuccess;
+    // Two gear passes side by side only fight for shared-memory bandwidth: a group's gear pass starts when the
+    // previous group's (on the other lane) is done, so that it runs beside that group's BLAKE3 pass instead.
+    if (gear_after) CU(cudaStreamWaitEvent(st, gear_after, 0));
+    launches += launch_gear(b, st, &gear_err);
+    if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
+    if (gear_done) CU(cudaEventRecord(gear_done, st));
+    if (timing) cudaEventRecord(lane->ev[1], st);
+    launches += launch_resolve(b, opt.range, st);
+    if (timing) cudaEventRecord(lane->ev[2], st);
+    if (!opt.resolve_only) {
+        launches += launch_chunk_hash(b, st);
+        launches += launch_gather(b, st);
+        if (timing) cudaEventRecord(lane->ev[3], st);
+        if (!opt.skip_merkle) launches += launch_merkle(b, st);
+        if (timing) cudaEventRecord(lane->ev[4], st);
+    } else {
+        launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
+                                    b.scalars + kScalarChunks, st);
         if (timing) {
-            cudaEventRecord(c->ev[6], st);
-            cudaEventSynchronize(c->ev[6]);
-            XetGpuTimings& t = c->last;
-            cudaEventElapsedTime(&t.gear_ms, c->ev[0], c->ev[1]);
-            cudaEventElapsedTime(&t.resolve_ms, c->ev[1], c->ev[2]);
-            cudaEventElapsedTime(&t.blake3_ms, c->ev[2], c->ev[3]);
-            cudaEventElapsedTime(&t.merkle_ms, c->ev[3], c->ev[4]);
-            cudaEventElapsedTime(&t.d2h_ms, c->ev[4], c->ev[6]);
-            cudaEventElapsedTime(&t.total_ms, c->ev[0], c->ev[6]);
-            t.gear_kernel_ms = t.leaf_kernel_ms = 0.f;
-            if (plan.n_tiles) cudaEventElapsedTime(&t.gear_kernel_ms, c->ev_kernel[0], c->ev_kernel[1]);
-            if (!opt.resolve_only && plan.n_slots && plan.n_groups_cap)
-                cudaEventElapsedTime(&t.leaf_kernel_ms, c->ev_kernel[2], c->ev_kernel[3]);
+            cudaEventRecord(lane->ev[3], st);
+            cudaEventRecord(lane->ev[4], st);
         }
-        c->last.bytes = total;
-        c->last.n_chunks = n_chunks;
-        c->last.n_candidates = n_cand;
-        c->last.kernel_launches = (uint32_t)launches;
+    }
+    CU(cudaGetLastError());
+    // readback: scalars, per-file counts, bases, roots, hashes
+    uint8_t* h_rb = lane->h_meta + (F + 1) * 24;
+    g->h_scalars = reinterpret_cast<uint64_t*>(h_rb);
+    g->h_base = g->h_scalars + 8;
+    g->h_count = reinterpret_cast<uint32_t*>(g->h_base + (F + 2));
+    g->h_hash = reinterpret_cast<uint8_t*>(g->h_count + (F + 1 + ((F + 1) & 1)));
+    g->h_root = g->h_hash + (F + 1) * 32;
+    CU(cudaMemcpyAsync(g->h_scalars, b.scalars, 64, cudaMemcpyDeviceToHost, st));
+    if (F) {
+        CU(cudaMemcpyAsync(g->h_base, b.file_chunk_base, (F + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(g->h_count, b.file_count, F * 4, cudaMemcpyDeviceToHost, st));
+        if (!opt.resolve_only && !opt.skip_merkle) {
+            CU(cudaMemcpyAsync(g->h_hash, b.file_hash, F * 32, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(g->h_root, b.file_root, F * 32, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    if (timing) cudaEventRecord(lane->ev[5], st);
+    g->launches = launches;
+    return nullptr;
+}
+
+// Result accumulator shared by all groups of one call.
+struct ResultBuilder {
+    std::vector<XetGpuFileResult> files;
+    std::vector<uint64_t> ends;
+    std::vector<uint8_t> hashes;
+    uint64_t n_cand = 0;
+    int launches = 0;
+    float gear_ms = 0, resolve_ms = 0, blake3_ms = 0, merkle_ms = 0, d2h_ms = 0, gear_kernel_ms = 0, leaf_kernel_ms = 0,
+          h2d_ms = 0;
+};
+
+// Wait for a group and collect its results.  *overflow = true when the candidate list was too small
+// (dense data): nothing is collected and the caller re-runs the group with the grown list.
+static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const uint64_t* offsets,
+                              const RunOptions& opt, ResultBuilder* rb, bool* overflow) {
+    const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
+    cudaStream_t st = lane->stream;
+    CU(cudaStreamSynchronize(st));
+    *overflow = false;
+    const Plan& plan = g->plan;
+    PipelineBuffers& b = g->b;
+    const size_t F = g->n_files;
+    const uint64_t n_cand = g->h_scalars[kScalarCand];
+    if (n_cand > plan.cand_cap) {
+        c->cand_cap_hint = std::max<uint64_t>(c->cand_cap_hint, n_cand + n_cand / 8 + 1024);
+        *overflow = true;
         return nullptr;
     }
+    const uint64_t n_chunks = F ? g->h_base[F] : 0;
+    if (opt.exit_cut_abs) {
+        uint64_t last = opt.range ? opt.range->walk_start : 0;
+        if (n_chunks)
+            CU(cudaMemcpy(&last, b.slot_end + (plan.slot_off[F - 1] + g->h_count[F - 1] - 1), 8, cudaMemcpyDeviceToHost));
+        *opt.exit_cut_abs = last;
+    }
+    const uint64_t chunk0 = rb->ends.size();
+    for (size_t f = 0; f < F; f++) {
+        XetGpuFileResult fr{};
+        if (!opt.resolve_only && !opt.skip_merkle) {
+            memcpy(fr.file_hash, g->h_hash + f * 32, 32);
+            memcpy(fr.merkle_root, g->h_root + f * 32, 32);
+        }
+        fr.size = offsets[f + 1] - offsets[f];
+        fr.n_chunks = g->h_count[f];
+        fr.first_chunk = (opt.want_chunks ? chunk0 : 0) + g->h_base[f];
+        rb->files.push_back(fr);
+    }
+    if (opt.want_chunks && n_chunks) {
+        rb->ends.resize(chunk0 + n_chunks);
+        rb->hashes.resize((chunk0 + n_chunks) * 32);
+        if (opt.resolve_only) {  // ends only: gather was skipped; single file in this mode
+            CU(cudaMemcpyAsync(rb->ends.data() + chunk0, b.slot_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+        } else {
+            CU(cudaMemcpyAsync(rb->ends.data() + chunk0, b.out_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(rb->hashes.data() + chunk0 * 32, b.out_hash, n_chunks * 32, cudaMemcpyDeviceToHost, st));
+        }
+        CU(cudaStreamSynchronize(st));
+        if (opt.end_bias)
+            for (uint64_t i = 0; i < n_chunks; i++) rb->ends[chunk0 + i] += opt.end_bias;
+    }
+    if (timing) {
+        cudaEventRecord(lane->ev[6], st);
+        cudaEventSynchronize(lane->ev[6]);
+        float t = 0;
+        cudaEventElapsedTime(&t, lane->ev[0], lane->ev[1]);
+        rb->gear_ms += t;
+        cudaEventElapsedTime(&t, lane->ev[1], lane->ev[2]);
+        rb->resolve_ms += t;
+        cudaEventElapsedTime(&t, lane->ev[2], lane->ev[3]);
+        rb->blake3_ms += t;
+        cudaEventElapsedTime(&t, lane->ev[3], lane->ev[4]);
+        rb->merkle_ms += t;
+        cudaEventElapsedTime(&t, lane->ev[4], lane->ev[6]);
+        rb->d2h_ms += t;
+        if (plan.n_tiles) {
+            cudaEventElapsedTime(&t, lane->ev_kernel[0], lane->ev_kernel[1]);
+            rb->gear_kernel_ms += t;
+        }
+        if (!opt.resolve_only && plan.n_slots && plan.n_groups_cap) {
+            cudaEventElapsedTime(&t, lane->ev_kernel[2], lane->ev_kernel[3]);
+            rb->leaf_kernel_ms += t;
+        }
+        if (g->had_h2d) {
+            cudaEventElapsedTime(&t, lane->ev[7], lane->ev[0]);
+            rb->h2d_ms += t;
+        }
+    }
+    rb->n_cand += n_cand;
+    rb->launches += g->launches;
+    return nullptr;
+}
+
+static XetError* build_result(const ResultBuilder& rb, bool want_chunks, XetGpuResult** out_result) {
+    if (!out_result) return nullptr;
+    XetGpuResult* r = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
+    if (!r) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+    r->n_files = rb.files.size();
+    r->files = (XetGpuFileResult*)calloc(rb.files.size() ? rb.files.size() : 1, sizeof(XetGpuFileResult));
+    if (!rb.files.empty()) memcpy(r->files, rb.files.data(), rb.files.size() * sizeof(XetGpuFileResult));
+    if (want_chunks && !rb.ends.empty()) {
+        r->n_chunks = rb.ends.size();
+        r->chunk_ends = (uint64_t*)malloc(rb.ends.size() * 8);
+        r->chunk_hashes = (uint8_t*)malloc(rb.hashes.size());
+        if (!r->chunk_ends || !r->chunk_hashes) {
+            xetgpu_free_result(r);
+            return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+        }
+        memcpy(r->chunk_ends, rb.ends.data(), rb.ends.size() * 8);
+        memcpy(r->chunk_hashes, rb.hashes.data(), rb.hashes.size());
+    }
+    *out_result = r;
+    return nullptr;
+}
+
+static void publish_timings(XetGpuContext* c, const ResultBuilder& rb, uint64_t bytes, float wall_ms) {
+    XetGpuTimings& t = c->last;
+    t.h2d_ms = rb.h2d_ms;
+    t.gear_ms = rb.gear_ms;
+    t.resolve_ms = rb.resolve_ms;
+    t.blake3_ms = rb.blake3_ms;
+    t.merkle_ms = rb.merkle_ms;
+    t.d2h_ms = rb.d2h_ms;
+    t.gear_kernel_ms = rb.gear_kernel_ms;
+    t.leaf_kernel_ms = rb.leaf_kernel_ms;
+    t.total_ms = wall_ms;
+    t.bytes = bytes;
+    t.n_chunks = 0;
+    for (const auto& f : rb.files) t.n_chunks += f.n_chunks;
+    t.n_candidates = rb.n_cand;
+    t.kernel_launches = (uint32_t)rb.launches;
+}
+
+// One group, synchronously, on lane 0 (also the retry path when the candidate list overflowed).
+static XetError* run_group_sync(XetGpuContext* c, Lane* lane, const uint8_t* d_data, const uint64_t* offsets,
+                                size_t n_files, const RunOptions& opt, ResultBuilder* rb) {
+    for (int attempt = 0; attempt < 3; attempt++) {
+        GroupState g;
+        if (XetError* e = launch_group(c, lane, d_data, offsets, n_files, opt, &g)) return e;
+        bool overflow = false;
+        if (XetError* e = finish_group(c, lane, &g, offsets, opt, rb, &overflow)) return e;
+        if (!overflow) return nullptr;
+    }
     return make_error(XETGPU_ERR_UNKNOWN, "candidate list kept overflowing");
+}
+
+static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uint64_t* offsets, size_t n_files,
+                              const RunOptions& opt, XetGpuResult** out_result) {
+    auto t0 = std::chrono::steady_clock::now();
+    ResultBuilder rb;
+    if (XetError* e = run_group_sync(c, &c->lanes[0], d_data, offsets, n_files, opt, &rb)) return e;
+    float wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    publish_timings(c, rb, n_files ? offsets[n_files] : 0, wall);
+    return build_result(rb, opt.want_chunks, out_result);
+}
+
+// ---- file groups on two lanes -------------------------------------------------------------------
+// A batch of several files can be cut into groups of whole files (>= 1/8 of the batch and >= 256 MiB each).
+// Group g runs on lane g % 2, so its host->device copy and its many small kernels overlap the previous
+// group's bulk kernels.
+struct HostSource {
+    const uint8_t* base = nullptr;  // host bytes of the batch; nullptr = bytes are already on the device
+};
+
+static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSource& host, const uint64_t* offsets,
+                           size_t n_files, const RunOptions& opt, XetGpuResult** out_result) {
+    const uint64_t total = n_files ? offsets[n_files] : 0;
+    const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
+    auto t0 = std::chrono::steady_clock::now();
+    // group boundaries (file indices)
+    std::vector<size_t> cut{0};
+    const uint64_t target = std::max<uint64_t>(total / 8, c->min_group_bytes);
+    // Measured on B200: two lanes pay off when there is a host->device copy to hide (+4 % end to end) or many
+    // files (+8 % on 10,000 files: the short latency-bound kernels of one group hide behind the other group's
+    // bulk kernels); a few large device-resident files run fastest as one group (the gear and BLAKE3 kernels
+    // each fill the SMs' shared memory, so they cannot be co-resident anyway).
+    const bool two_lanes = !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && (host.base != nullptr || n_files >= 16);
+    if (two_lanes) {
+        uint64_t acc = 0;
+        for (size_t f = 0; f < n_files; f++) {
+            acc += offsets[f + 1] - offsets[f];
+            if (acc >= target && f + 1 < n_files && total - offsets[f + 1] >= c->min_group_bytes / 2) {
+                cut.push_back(f + 1);
+                acc = 0;
+            }
+        }
+    }
+    cut.push_back(n_files);
+    const size_t G = cut.size() - 1;
+    ResultBuilder rb;
+    auto ingest = [&](Lane* lane, uint64_t lo, uint64_t hi, GroupState* g) -> XetError* {
+        if (!host.base || hi == lo) return nullptr;
+        if (timing) cudaEventRecord(lane->ev[7], lane->stream);
+        g->had_h2d = true;
+        return ingest_host(c, lane->stream, host.base + lo, hi - lo, const_cast<uint8_t*>(d_data) + lo);
+    };
+    if (G <= 1) {
+        GroupState dummy;
+        if (XetError* e = ingest(&c->lanes[0], 0, total, &dummy)) return e;
+        // the copy is on lane 0's stream, in front of the pipeline: timing of it is taken there
+        for (int attempt = 0; attempt < 3; attempt++) {
+            GroupState g;
+            g.had_h2d = dummy.had_h2d && attempt == 0;
+            if (XetError* e = launch_group(c, &c->lanes[0], d_data, offsets, n_files, opt, &g)) return e;
+            bool overflow = false;
+            if (XetError* e = finish_group(c, &c->lanes[0], &g, offsets, opt, &rb, &overflow)) return e;
+            if (!overflow) break;
+            if (attempt == 2) return make_error(XETGPU_ERR_UNKNOWN, "candidate list kept overflowing");
+        }
+    } else {
+        // lane 1 must see what the caller enqueued on the context's stream before this call
+        CU(cudaEventRecord(c->ev_fork, c->stream));
+        CU(cudaStreamWaitEvent(c->lanes[1].stream, c->ev_fork, 0));
+        GroupState state[2];
+        std::vector<uint64_t> rel[2];
+        uint64_t group_base[2] = {0, 0};
+        long pending[2] = {-1, -1};
+        auto finish = [&](int li) -> XetError* {
+            if (pending[li] < 0) return nullptr;
+            const size_t gi = (size_t)pending[li];
+            pending[li] = -1;
+            bool overflow = false;
+            if (XetError* e = finish_group(c, &c->lanes[li], &state[li], rel[li].data(), opt, &rb, &overflow)) return e;
+            if (overflow)  // dense candidates: redo this group alone with the grown list
+                return run_group_sync(c, &c->lanes[li], d_data + group_base[li], rel[li].data(),
+                                      cut[gi + 1] - cut[gi], opt, &rb);
+            return nullptr;
+        };
+        for (size_t gi = 0; gi < G; gi++) {
+            const int li = (int)(gi & 1);
+            // results are collected in group order: the other lane's older group first
+            if (gi >= 2)
+                if (XetError* e = finish(li)) return e;
+            const size_t f0 = cut[gi], f1 = cut[gi + 1];
+            // the group's device base must stay 16-byte aligned (TMA): start it at the aligned address at or
+            // below its first file; the few bytes of the previous file in front are ignored by every kernel
+            const uint64_t base_lo = offsets[f0] & ~15ull;
+            group_base[li] = base_lo;
+            rel[li].assign(f1 - f0 + 1, 0);
+            for (size_t f = f0; f <= f1; f++) rel[li][f - f0] = offsets[f] - base_lo;
+            state[li] = GroupState{};
+            if (XetError* e = ingest(&c->lanes[li], offsets[f0], offsets[f1], &state[li])) return e;
+            if (XetError* e = launch_group(c, &c->lanes[li], d_data + base_lo, rel[li].data(), f1 - f0, opt, &state[li],
+                                           gi ? c->ev_gear_done[li ^ 1] : nullptr, c->ev_gear_done[li]))
+                return e;
+            pending[li] = (long)gi;
+        }
+        const int first = pending[0] >= 0 && (pending[1] < 0 || pending[0] < pending[1]) ? 0 : 1;
+        if (XetError* e = finish(first)) return e;
+        if (XetError* e = finish(first ^ 1)) return e;
+    }
+    float wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    publish_timings(c, rb, total, wall);
+    return build_result(rb, opt.want_chunks, out_result);
 }
 
 static XetError* resolve_memory_kind(const void* data, int32_t memory, bool* is_device) {
@@ -603,35 +838,36 @@ static XetError* resolve_memory_kind(const void* data, int32_t memory, bool* is_
     return nullptr;
 }
 
-// Brings [data+lo, data+hi) onto the device if needed.  Returns a 16-byte aligned device pointer
-// d such that d[0] is data[lo] ... plus the offset shift to apply.
+// Device inputs: returns a 16-byte aligned device pointer to data[lo] (copying once, device to device,
+// if the caller's pointer is not aligned).  Host inputs: returns the context's device input buffer,
+// sized for hi - lo bytes; the bytes are copied later, group by group (run_batch).
 static XetError* stage_input(XetGpuContext* c, const void* data, uint64_t lo, uint64_t hi, int32_t memory,
-                             const uint8_t** d_out) {
+                             const uint8_t** d_out, bool* is_host) {
     bool is_device = false;
     if (XetError* e = resolve_memory_kind(data, memory, &is_device)) return e;
     const uint8_t* p = (const uint8_t*)data + lo;
-    const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
-    c->last.h2d_ms = 0.f;
+    *is_host = !is_device;
     if (is_device) {
         if (((uintptr_t)p & 15u) == 0) {
             *d_out = p;
             return nullptr;
         }
-        // unaligned device input: one device-to-device copy into the aligned input buffer
         if (XetError* e = ensure_input(c, hi - lo)) return e;
         CU(cudaMemcpyAsync(c->d_input, p, hi - lo, cudaMemcpyDeviceToDevice, c->stream));
         *d_out = c->d_input;
         return nullptr;
     }
     if (XetError* e = ensure_input(c, hi - lo)) return e;
-    if (timing) cudaEventRecord(c->ev[7], c->stream);
-    if (XetError* e = ingest_host(c, p, hi - lo, c->d_input)) return e;
-    if (timing) {
-        cudaEventRecord(c->ev[6], c->stream);
-        cudaEventSynchronize(c->ev[6]);
-        cudaEventElapsedTime(&c->last.h2d_ms, c->ev[7], c->ev[6]);
-    }
     *d_out = c->d_input;
+    return nullptr;
+}
+
+// stage_input + the host->device copy on the context's stream (single-group callers).
+static XetError* stage_input_now(XetGpuContext* c, const void* data, uint64_t lo, uint64_t hi, int32_t memory,
+                                 const uint8_t** d_out) {
+    bool is_host = false;
+    if (XetError* e = stage_input(c, data, lo, hi, memory, d_out, &is_host)) return e;
+    if (is_host) return ingest_host(c, c->stream, (const uint8_t*)data + lo, hi - lo, c->d_input);
     return nullptr;
 }
 
@@ -652,11 +888,15 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
     const uint64_t lo = n_files ? offsets[0] : 0;
     for (size_t f = 0; f <= n_files && n_files; f++) rel[f] = offsets[f] - lo;
     const uint8_t* d = nullptr;
-    if (n_files && rel[n_files])
-        if (XetError* e = stage_input(c, data, lo, offsets[n_files], memory, &d)) return e;
+    HostSource host;
+    if (n_files && rel[n_files]) {
+        bool is_host = false;
+        if (XetError* e = stage_input(c, data, lo, offsets[n_files], memory, &d, &is_host)) return e;
+        if (is_host) host.base = (const uint8_t*)data + lo;
+    }
     RunOptions opt;
     opt.want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
-    return run_pipeline(c, d, rel.data(), n_files, opt, out_result);
+    return run_batch(c, d, host, rel.data(), n_files, opt, out_result);
 }
 
 // -------------------------------------------------------------------------------------- files
@@ -832,12 +1072,12 @@ extern "C" XetError* xetgpu_gear_candidates(XetGpuContext* c, const void* data, 
     CU(cudaSetDevice(c->device));
     if (len == 0) return nullptr;
     const uint8_t* d = nullptr;
-    if (XetError* e = stage_input(c, data, 0, len, memory, &d)) return e;
+    if (XetError* e = stage_input_now(c, data, 0, len, memory, &d)) return e;
     uint64_t offsets[2] = {0, len};
     for (int attempt = 0; attempt < 3; attempt++) {
         Plan plan = make_plan(offsets, 1, len, c->cand_cap_hint);
         PipelineBuffers b{};
-        if (XetError* e = ensure_workspace(c, plan, &b)) return e;
+        if (XetError* e = ensure_workspace(&c->lanes[0], plan, &b)) return e;
         b.data = d;
         CU(cudaMemsetAsync(b.scalars, 0, 64, c->stream));
         b.sm_count = c->sm_count;
@@ -879,7 +1119,7 @@ static XetError* range_common(XetGpuContext* c, const void* data, int32_t memory
     if (len && !data) return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
     const uint8_t* d = nullptr;
     if (len)
-        if (XetError* e = stage_input(c, data, 0, len, memory, &d)) return e;
+        if (XetError* e = stage_input_now(c, data, 0, len, memory, &d)) return e;
     uint64_t offsets[2] = {0, len};
     RangeWalk rw{entry_cut - data_pos, range_end == file_len ? 1u : 0u};
     RunOptions opt;
@@ -926,7 +1166,7 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
     plan.cand_cap = 1;
     plan.max_nodes = n_chunks + 1;
     PipelineBuffers b{};
-    if (XetError* e = ensure_workspace(c, plan, &b)) return e;
+    if (XetError* e = ensure_workspace(&c->lanes[0], plan, &b)) return e;
     cudaStream_t st = c->stream;
     uint64_t h_slot[2] = {0, n_chunks + 1};
     uint32_t cnt = (uint32_t)n_chunks;

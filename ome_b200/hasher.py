@@ -18,6 +18,7 @@ from . import _lib as L
 MEM_AUTO, MEM_HOST, MEM_DEVICE = 0, 1, 2
 WANT_CHUNKS = 1
 CTX_STAGE_TIMING = 1
+CTX_NO_OVERLAP = 2
 
 MIN_CHUNK, TARGET_CHUNK, MAX_CHUNK = 8192, 65536, 131072
 RANGE_LEAD = MAX_CHUNK + 64
@@ -124,10 +125,10 @@ class XetHasher:
     """One context on one GPU.  Thread-compatible like the reference client: calls serialise."""
 
     def __init__(self, device: int = -1, stream: int = 0, staging_bytes: int = 0, max_batch_bytes: int = 0,
-                 stage_timing: bool = False):
+                 stage_timing: bool = False, overlap: bool = True):
         self._lib = L.load()
         cfg = L.XetGpuConfig(device, stream or None, staging_bytes, max_batch_bytes,
-                             CTX_STAGE_TIMING if stage_timing else 0)
+                             (CTX_STAGE_TIMING if stage_timing else 0) | (0 if overlap else CTX_NO_OVERLAP))
         ctx = L.CTX()
         _check(self._lib.xetgpu_context_new(C.byref(cfg), C.byref(ctx)))
         self._ctx = ctx

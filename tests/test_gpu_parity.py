@@ -324,3 +324,38 @@ def test_xetsum_cli_cpp_consumer(tmp_path):
     ch = subprocess.run([exe, "--chunks", paths[3]], capture_output=True, text=True, check=True).stdout.splitlines()
     assert len(ch) == 1 + cases["splitmix_seed1_1MiB"]["n_chunks"]
     assert ch[1].split() == ["25125", cases["splitmix_seed1_1MiB"]["chunk_hashes"][0]]
+
+
+@pytest.fixture()
+def small_group_hasher(monkeypatch):
+    """A context whose file groups are tiny, so that ordinary test batches take the two-lane path
+    (groups alternating between two streams, unaligned group starts, staggered gear passes)."""
+    import ome_b200
+    monkeypatch.setenv("XETGPU_MIN_GROUP_BYTES", str(1 << 20))
+    h = ome_b200.XetHasher(stage_timing=True)
+    yield h
+    h.close()
+
+
+@pytest.mark.parametrize("where", ["host", "device"])
+def test_two_lane_file_groups(small_group_hasher, where):
+    import torch
+    rng = np.random.default_rng(23)
+    # >= 16 files: device-resident batches take the two-lane path too
+    sizes = [int(x) for x in np.exp(rng.uniform(np.log(1000), np.log(6e6), 40))] + [0, 1, 8191, 3 << 20, 5 << 20]
+    datas = [xet_inputs.splitmix_bytes(1500 + i, n) for i, n in enumerate(sizes)]
+    # one group of dense candidates in the middle: its candidate list overflows and is re-run alone
+    datas[20] = xet_inputs.build([["repeat", xet_inputs.W_HEX, 30000]])
+    sizes[20] = datas[20].size
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+    packed = np.concatenate(datas)
+    src = torch.from_numpy(packed).cuda() if where == "device" else packed
+    cl = small_group_hasher.hash_buffers(src, offsets, want_chunks=True)
+    assert len(cl.files) == len(sizes)
+    for f, d in enumerate(datas):
+        check_against_oracle(cl, f, d)
+    t = small_group_hasher.last_timings()
+    assert t["n_chunks"] == sum(f.n_chunks for f in cl.files) and t["bytes"] == packed.size
+    # and without chunk lists (first_chunk bookkeeping differs)
+    cl2 = small_group_hasher.hash_buffers(src, offsets)
+    assert [f.file_hash for f in cl2.files] == [f.file_hash for f in cl.files]
