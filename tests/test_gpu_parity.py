@@ -359,3 +359,43 @@ def test_two_lane_file_groups(small_group_hasher, where):
     # and without chunk lists (first_chunk bookkeeping differs)
     cl2 = small_group_hasher.hash_buffers(src, offsets)
     assert [f.file_hash for f in cl2.files] == [f.file_hash for f in cl.files]
+
+
+def test_randomised_inputs_against_oracle(hasher):
+    """Seeded fuzz: files stitched from random, zero, periodic and dense-candidate pieces of random
+    lengths, hashed in one batch; every boundary and hash must equal the oracle's."""
+    rng = np.random.default_rng(20261106)
+    kinds = ["splitmix", "zeros", "mod251", "W"]
+    datas = []
+    for i in range(48):
+        spec = []
+        for _ in range(int(rng.integers(1, 5))):
+            k = kinds[int(rng.integers(0, 4))]
+            n = int(np.exp(rng.uniform(np.log(1), np.log(2.5e6))))
+            if k == "splitmix":
+                spec.append(["splitmix", int(rng.integers(0, 1 << 30)), n])
+            elif k == "W":
+                spec.append(["repeat", xet_inputs.W_HEX, max(1, n // 64)])
+            else:
+                spec.append([k, n])
+        datas.append(xet_inputs.build(spec))
+    offsets = np.concatenate([[0], np.cumsum([d.size for d in datas])]).astype(np.uint64)
+    cl = hasher.hash_buffers(np.concatenate(datas), offsets, want_chunks=True)
+    for f, d in enumerate(datas):
+        check_against_oracle(cl, f, d)
+
+
+def test_context_shared_by_threads(hasher):
+    """Calls on one context serialise (pkg/xet/README.md:76,88 says the same of the reference client)."""
+    import threading
+    datas = [xet_inputs.splitmix_bytes(3000 + i, (1 << 20) + 1000 * i) for i in range(8)]
+    want = [xet_oracle.hash_file(d).file_hash for d in datas]
+    got = [None] * len(datas)
+
+    def work(i):
+        got[i] = hasher.hash_bytes(datas[i]).files[0].file_hash
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(datas))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert got == want
