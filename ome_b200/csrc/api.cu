@@ -15,8 +15,11 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -107,6 +110,11 @@ struct XetGpuContext {
     uint64_t d_input_cap = 0;
     uint8_t* h_stage[2] = {nullptr, nullptr};  // pinned ingestion buffers
     cudaEvent_t stage_free[2] = {nullptr, nullptr};
+    // file ingestion: ring of pinned read slots filled by reader threads (xetgpu_hash_files)
+    std::vector<uint8_t*> read_slots;
+    std::vector<cudaEvent_t> read_slot_ev;
+    uint64_t read_slot_bytes = 16ull << 20;
+    size_t read_threads = 8;
     uint64_t cand_cap_hint = 0;
     XetGpuTimings last = {};
     // progress
@@ -115,6 +123,8 @@ struct XetGpuContext {
     uint32_t throttle_ms = 0;
     std::chrono::steady_clock::time_point last_progress;
 };
+
+constexpr size_t kReadSlots = 16;  // pinned 16 MiB slots of the file reader ring
 
 typedef XetGpuContext::Lane Lane;
 
@@ -162,6 +172,7 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
     if (config) {
         c->flags = config->flags;
         if (config->staging_bytes) c->staging_bytes = (config->staging_bytes + 4095) & ~4095ull;
+        if (config->staging_bytes) c->read_slot_bytes = std::min<uint64_t>(c->staging_bytes, 64ull << 20);
         if (config->max_batch_bytes) c->max_batch_bytes = config->max_batch_bytes;
         c->stream = (cudaStream_t)config->stream;
     }
@@ -193,6 +204,14 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
         delete c;
         return cuda_error(le, "kernel attribute setup");
     }
+    {
+        unsigned hc = std::thread::hardware_concurrency();
+        c->read_threads = hc ? std::min<size_t>(kReadSlots, hc) : 4;
+        if (const char* v = getenv("XETGPU_READ_THREADS")) {
+            unsigned long n = strtoul(v, nullptr, 10);
+            if (n) c->read_threads = std::min<size_t>(n, 64);
+        }
+    }
     *out_ctx = c;
     return nullptr;
 }
@@ -217,6 +236,8 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
     if (c->d_input) cudaFree(c->d_input);
     for (auto& p : c->h_stage)
         if (p) cudaFreeHost(p);
+    for (auto& p : c->read_slots) cudaFreeHost(p);
+    for (auto& ev : c->read_slot_ev) cudaEventDestroy(ev);
     for (auto& ev : c->stage_free)
         if (ev) cudaEventDestroy(ev);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -900,16 +921,90 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
 }
 
 // -------------------------------------------------------------------------------------- files
-static XetError* read_fully(int fd, uint8_t* dst, uint64_t n, const char* path) {
-    uint64_t got = 0;
-    while (got < n) {
-        ssize_t r = read(fd, dst + got, n - got);
-        if (r < 0) {
-            if (errno == EINTR) continue;
-            return make_error(XETGPU_ERR_IO, std::string("read failed: ") + strerror(errno), path);
+// File ingestion.  A single read() loop moves ~5 GB/s out of the page cache — no faster than the CPU
+// reference hashes — so a batch is cut into pieces that a small pool of reader threads pread() into a
+// ring of pinned slots; the thread that filled a slot enqueues its host->device copy itself (the
+// copies land in disjoint device ranges, so their order on the stream does not matter) and the slot
+// is reused once that copy's event has fired.
+struct ReadPiece {
+    int fd;
+    uint64_t file_off, len, dev_off;
+    size_t file;  // index into paths (for error text)
+};
+
+struct ReaderPool {
+    XetGpuContext* c = nullptr;
+    const char* const* paths = nullptr;
+    std::vector<ReadPiece> pieces;
+    std::vector<uint8_t*> slots;
+    std::vector<cudaEvent_t> slot_ev;
+    std::vector<long> slot_issued;  // index of the last piece whose copy was enqueued from this slot (-1: none)
+    std::mutex mu;
+    std::condition_variable cv;
+    std::atomic<size_t> next{0};
+    std::atomic<uint64_t> bytes_done{0};
+    std::atomic<bool> stop{false};
+    XetError* err = nullptr;
+
+    void fail(XetError* e) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!err) err = e;
+        else xetgpu_free_error(e);
+        stop = true;
+        cv.notify_all();
+    }
+
+    void worker() {
+        cudaSetDevice(c->device);
+        const size_t S = slots.size();
+        while (!stop) {
+            const size_t i = next.fetch_add(1);
+            if (i >= pieces.size()) return;
+            const size_t s = i % S;
+            {   // the slot is free once the piece that used it last (i - S) has enqueued its copy ...
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || slot_issued[s] == (long)i - (long)S; });
+                if (stop) return;
+            }
+            if (i >= S) cudaEventSynchronize(slot_ev[s]);  // ... and that copy has drained
+            const ReadPiece& p = pieces[i];
+            uint64_t got = 0;
+            while (got < p.len) {
+                ssize_t r = pread(p.fd, slots[s] + got, p.len - got, (off_t)(p.file_off + got));
+                if (r < 0 && errno == EINTR) continue;
+                if (r <= 0) {
+                    fail(make_error(XETGPU_ERR_IO, r < 0 ? std::string("read failed: ") + strerror(errno)
+                                                          : std::string("file shrank while being read"),
+                                    paths[p.file]));
+                    return;
+                }
+                got += (uint64_t)r;
+            }
+            cudaError_t ce = cudaMemcpyAsync(c->d_input + p.dev_off, slots[s], p.len, cudaMemcpyHostToDevice, c->stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(slot_ev[s], c->stream);
+            if (ce != cudaSuccess) {
+                fail(cuda_error(ce, "cudaMemcpyAsync(H2D)"));
+                return;
+            }
+            bytes_done += p.len;
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                slot_issued[s] = (long)i;
+            }
+            cv.notify_all();
         }
-        if (r == 0) return make_error(XETGPU_ERR_IO, "file shrank while being read", path);
-        got += (uint64_t)r;
+    }
+};
+
+static XetError* ensure_read_slots(XetGpuContext* c) {
+    if (c->read_slots.size() == kReadSlots) return nullptr;
+    for (size_t i = c->read_slots.size(); i < kReadSlots; i++) {
+        uint8_t* p = nullptr;
+        CU(cudaMallocHost((void**)&p, c->read_slot_bytes));
+        cudaEvent_t ev;
+        CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        c->read_slots.push_back(p);
+        c->read_slot_ev.push_back(ev);
     }
     return nullptr;
 }
@@ -921,7 +1016,7 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
     *out_result = nullptr;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    if (XetError* e = ensure_staging(c)) return e;
+    if (XetError* e = ensure_read_slots(c)) return e;
     std::vector<uint64_t> sizes(n_files);
     uint64_t all_bytes = 0;
     for (size_t f = 0; f < n_files; f++) {
@@ -944,6 +1039,7 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
     pu.phase = XET_PROGRESS_PHASE_SCANNING;
     pu.total_bytes = all_bytes;
     pu.total_files = (uint32_t)n_files;
+    uint64_t bytes_before = 0;
     XetError* err = nullptr;
     size_t f0 = 0;
     while (f0 < n_files && !err) {
@@ -952,44 +1048,55 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
         uint64_t bytes = 0;
         while (f1 < n_files && (f1 == f0 || bytes + sizes[f1] <= c->max_batch_bytes)) bytes += sizes[f1++];
         if ((err = ensure_input(c, bytes))) break;
+        if (cancel && cancel->callback && cancel->callback(cancel->user_data)) {
+            err = make_error(XETGPU_ERR_CANCELLED, "cancelled");
+            break;
+        }
         std::vector<uint64_t> rel(f1 - f0 + 1, 0);
+        ReaderPool pool;
+        pool.c = c;
+        pool.paths = paths;
+        pool.slots = c->read_slots;
+        pool.slot_ev = c->read_slot_ev;
+        pool.slot_issued.assign(kReadSlots, -1);
+        for (size_t s = 0; s < kReadSlots; s++) pool.slot_issued[s] = (long)s - (long)kReadSlots;
+        std::vector<int> fds;
         uint64_t dev_off = 0;
-        int buf = 0;
-        for (size_t f = f0; f < f1 && !err; f++) {
-            if (cancel && cancel->callback && cancel->callback(cancel->user_data)) {
-                err = make_error(XETGPU_ERR_CANCELLED, "cancelled");
-                break;
-            }
+        for (size_t f = f0; f < f1; f++) {
             rel[f - f0] = dev_off;
-            int fd = open(paths[f], O_RDONLY);
-            if (fd < 0) {
+            int fd = sizes[f] ? open(paths[f], O_RDONLY) : -1;
+            if (sizes[f] && fd < 0) {
                 err = make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
                                  std::string("cannot open file: ") + strerror(errno), paths[f]);
                 break;
             }
-            pu.current_file = paths[f];
-            pu.current_file_total_bytes = sizes[f];
-            for (uint64_t o = 0; o < sizes[f] && !err; o += c->staging_bytes, buf ^= 1) {
-                uint64_t n = std::min<uint64_t>(c->staging_bytes, sizes[f] - o);
-                cudaEventSynchronize(c->stage_free[buf]);
-                if ((err = read_fully(fd, c->h_stage[buf], n, paths[f]))) break;
-                cudaError_t ce = cudaMemcpyAsync(c->d_input + dev_off + o, c->h_stage[buf], n, cudaMemcpyHostToDevice,
-                                                 c->stream);
-                if (ce != cudaSuccess) {
-                    err = cuda_error(ce, "cudaMemcpyAsync(H2D)");
-                    break;
-                }
-                cudaEventRecord(c->stage_free[buf], c->stream);
-                pu.completed_bytes += n;
-                pu.current_file_completed_bytes = o + n;
-                report_progress(c, pu, false);
-            }
-            close(fd);
+            if (fd >= 0) fds.push_back(fd);
+            for (uint64_t o = 0; o < sizes[f]; o += c->read_slot_bytes)
+                pool.pieces.push_back(ReadPiece{fd, o, std::min<uint64_t>(c->read_slot_bytes, sizes[f] - o), dev_off + o, f});
             dev_off += sizes[f];
-            pu.completed_files++;
         }
-        if (err) break;
         rel[f1 - f0] = dev_off;
+        if (!err && !pool.pieces.empty()) {
+            const size_t nthreads = std::min<size_t>(std::min<size_t>(c->read_threads, pool.pieces.size()), kReadSlots);
+            std::vector<std::thread> threads;
+            for (size_t t = 0; t < nthreads; t++) threads.emplace_back([&pool] { pool.worker(); });
+            // this thread reports progress and polls for cancellation while the readers work
+            while (pool.next.load() < pool.pieces.size() && !pool.stop) {
+                std::this_thread::sleep_for(std::chrono::milliseconds(5));
+                pu.completed_bytes = bytes_before + pool.bytes_done.load();
+                report_progress(c, pu, false);
+                if (cancel && cancel->callback && cancel->callback(cancel->user_data))
+                    pool.fail(make_error(XETGPU_ERR_CANCELLED, "cancelled"));
+            }
+            for (auto& t : threads) t.join();
+            err = pool.err;
+        }
+        for (int fd : fds) close(fd);
+        if (err) break;
+        bytes_before += bytes;
+        pu.completed_bytes = bytes_before;
+        pu.completed_files = (uint32_t)f1;
+        report_progress(c, pu, false);
         RunOptions opt;
         opt.want_chunks = want_chunks;
         XetGpuResult* part = nullptr;
