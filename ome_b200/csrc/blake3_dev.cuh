@@ -45,6 +45,29 @@ __device__ __forceinline__ uint32_t fma_add(uint32_t x, uint32_t y, uint32_t one
     return r;
 }
 
+// A rotate can also run on the FMA pipe: x * 2^(32-n) as a 64-bit product holds x >> n in its high word and
+// x << (32-n) in its low word; their sum is the rotation.  IMAD.WIDE issues at half rate, so this costs
+// three FMA slots instead of one ALU slot — worth it only for as many rotates as balance the two pipes
+// (ALU ~533 slots vs FMA ~365 per compression): XG_GF uses it for the rotate by 16.
+__device__ __forceinline__ uint32_t rotr_fma(uint32_t x, uint32_t pow2, uint32_t one) {
+    uint32_t lo, hi, r;
+    asm("{\n\t.reg .u64 t;\n\tmul.wide.u32 t, %2, %3;\n\tmov.b64 {%0, %1}, t;\n\t}" : "=r"(lo), "=r"(hi) : "r"(x), "r"(pow2));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(one), "r"(hi));
+    return r;
+}
+
+#define XG_GF(a, b, c, d, mx, my)             \
+    do {                                      \
+        a = fma_add(fma_add(a, (mx), one), b, one); \
+        d = rotr_fma(d ^ a, p16, one);        \
+        c = fma_add(c, d, one);               \
+        b = rotr12(b ^ c);                    \
+        a = fma_add(fma_add(a, (my), one), b, one); \
+        d = rotr8(d ^ a);                     \
+        c = fma_add(c, d, one);               \
+        b = rotr7(b ^ c);                     \
+    } while (0)
+
 #define XG_G(a, b, c, d, mx, my)              \
     do {                                      \
         a = fma_add(fma_add(a, (mx), one), b, one); \
@@ -57,16 +80,28 @@ __device__ __forceinline__ uint32_t fma_add(uint32_t x, uint32_t y, uint32_t one
         b = rotr7(b ^ c);                     \
     } while (0)
 
+// Measured on B200: with 28 of the 448 rotates per compression on the FMA pipe the leaf kernel is 2.5 % SLOWER
+// (8.69 -> 8.91 ms per 16 GB): the extra instruction per rotate costs more issue slots than the ALU slot it frees.
+// Kept for reference, off by default.
+#ifndef XG_FMA_ROT
+#define XG_FMA_ROT 0
+#endif
+#if XG_FMA_ROT
+#define XG_G0 XG_GF
+#else
+#define XG_G0 XG_G
+#endif
+
 // One round with message word indices given as literals.
 #define XG_ROUND(i0, i1, i2, i3, i4, i5, i6, i7, i8, i9, i10, i11, i12, i13, i14, i15) \
     do {                                                                                \
-        XG_G(v0, v4, v8, v12, m[i0], m[i1]);                                            \
+        XG_G0(v0, v4, v8, v12, m[i0], m[i1]);                                           \
         XG_G(v1, v5, v9, v13, m[i2], m[i3]);                                            \
-        XG_G(v2, v6, v10, v14, m[i4], m[i5]);                                           \
+        XG_G0(v2, v6, v10, v14, m[i4], m[i5]);                                          \
         XG_G(v3, v7, v11, v15, m[i6], m[i7]);                                           \
-        XG_G(v0, v5, v10, v15, m[i8], m[i9]);                                           \
+        XG_G0(v0, v5, v10, v15, m[i8], m[i9]);                                          \
         XG_G(v1, v6, v11, v12, m[i10], m[i11]);                                         \
-        XG_G(v2, v7, v8, v13, m[i12], m[i13]);                                          \
+        XG_G0(v2, v7, v8, v13, m[i12], m[i13]);                                         \
         XG_G(v3, v4, v9, v14, m[i14], m[i15]);                                          \
     } while (0)
 
@@ -80,6 +115,7 @@ __device__ __forceinline__ void b3_compress(uint32_t (&cv)[8], const uint32_t (&
     uint32_t v8 = XG_IV0, v9 = XG_IV1, v10 = XG_IV2, v11 = XG_IV3;
     uint32_t v12 = counter_lo, v13 = counter_hi, v14 = block_len, v15 = flags;
     const uint32_t one = c_b3_one;
+    const uint32_t p16 = c_b3_one << 16;  // 2^16, opaque to the assembler like `one`
     // message schedule = repeated application of the BLAKE3 permutation
     XG_ROUND(0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15);
     XG_ROUND(2, 6, 3, 10, 7, 0, 4, 13, 1, 11, 12, 5, 9, 14, 15, 8);
