@@ -173,12 +173,21 @@ def splice_at_common_cut(fix_ends, fix_hashes, spec_ends, spec_hashes):
 
 
 def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end: int, group=None,
-                        comm_device: Optional[torch.device] = None) -> RangeOutcome:
+                        comm_device: Optional[torch.device] = None, phases: Optional[dict] = None) -> RangeOutcome:
     """`piece` holds bytes [begin - lead, end) of the file (tensor / array / buffer the engine accepts,
     sliceable).  Collective over `group`: ranks must call it with consecutive ranges in rank order."""
+    import time as _time
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     dev = comm_device or torch.device("cpu")
     rehashed = 0
+    _t = [_time.perf_counter()]
+
+    def _mark(name):
+        if phases is not None:
+            now = _time.perf_counter()
+            phases[name] = phases.get(name, 0.0) + (now - _t[0]) * 1e3
+            _t[0] = now
+
     # 2. speculative pass over the whole range (rank 0's entry is the true one: the file start)
     assumed = 0 if rank == 0 else begin
     if end > begin or rank == 0:
@@ -186,6 +195,7 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
         ends, hashes, exit_cut = spec.chunk_ends, spec.chunk_hashes, spec.exit_cut
     else:                                          # empty range: owns no chunk, only passes the carry on
         ends, hashes, exit_cut = np.zeros(0, dtype=np.uint64), np.zeros((0, 32), dtype=np.uint8), assumed
+    _mark("speculative_pass_ms")
     # 3. carry chain
     if rank > 0:
         true_entry = _recv_int(rank - 1, dev, group)
@@ -208,6 +218,7 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
     if rank + 1 < world:
         _send_int(int(exit_cut), rank + 1, dev, group)
     out = RangeOutcome(ends, hashes, int(exit_cut), rehashed)
+    _mark("carry_chain_ms")
     # 4. chunk lists to rank 0
     counts = torch.zeros(world, dtype=torch.int64, device=dev)
     counts[rank] = ends.size
@@ -229,9 +240,12 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
         e = np.concatenate(all_e)
         h = np.concatenate(all_h)
         sizes = np.diff(np.concatenate([[0], e])).astype(np.uint64)
+        _mark("gather_ms")
         out.merkle_root, out.file_hash = engine.merkle_from_chunks(h, sizes)
         out.n_chunks_total = int(e.size)
+        _mark("merkle_ms")
     elif ends.size:
         dist.send(mine_e, _peer(0, group), group=group)
         dist.send(mine_h, _peer(0, group), group=group)
+        _mark("gather_ms")
     return out

@@ -101,6 +101,8 @@ def cases(large):
     add("safetensors_shaped_2MiB",
         [["hex", len(hdr).to_bytes(8, "little").hex()], ["hex", hdr.hex()], ["splitmix", 10, 2 * MiB]])
     if large:
+        # BASELINE config 1 size: 1 GiB (SURVEY.md Appendix B lists this one as an hf_xet-only vector)
+        add("one_GiB_16x64MiB_splitmix_seeds_100_115", [["splitmix", 100 + i, 64 * MiB] for i in range(16)], large=True)
         add("gt_4GiB_splitmix3_then_zeros", [["splitmix", 3, MiB], ["zeros", 4831838208 - MiB]], large=True)
     return c
 
