@@ -407,3 +407,17 @@ def test_context_shared_by_threads(hasher):
     [t.start() for t in ts]
     [t.join() for t in ts]
     assert got == want
+
+
+def test_degenerate_batches(hasher):
+    """No files at all; only empty files; an empty file between non-empty ones."""
+    cl = hasher.hash_buffers(b"", [0], want_chunks=True)
+    assert cl.files == [] and cl.chunk_ends.size == 0
+    cl = hasher.hash_buffers(b"", [0, 0, 0, 0], want_chunks=True)
+    assert [f.file_hash for f in cl.files] == [bytes(32)] * 3 and all(f.n_chunks == 0 for f in cl.files)
+    d = xet_inputs.splitmix_bytes(9, 300000)
+    cl = hasher.hash_buffers(np.concatenate([d, d]), [0, 300000, 300000, 600000], want_chunks=True)
+    check_against_oracle(cl, 0, d)
+    assert cl.files[1].n_chunks == 0 and cl.files[1].file_hash == bytes(32)
+    check_against_oracle(cl, 2, d)
+    assert hasher.gear_candidates(b"").size == 0
