@@ -368,8 +368,28 @@ __global__ void __launch_bounds__(kScanThreads)
     }
 }
 
+// Small inputs (the per-file and per-segment arrays of small batches): one CTA, one launch.
+__global__ void __launch_bounds__(1024) scan_small_kernel(const uint32_t* __restrict__ in, uint64_t n,
+                                                           uint64_t* __restrict__ out, uint64_t* __restrict__ total_out) {
+    __shared__ uint64_t s_warp[32];
+    uint64_t carry = 0;
+    for (uint64_t start = 0; start <= n; start += 1024) {
+        const uint64_t i = start + threadIdx.x;
+        const uint64_t v = i < n ? in[i] : 0;
+        uint64_t tot;
+        const uint64_t ex = block_exclusive_scan(v, s_warp, &tot);
+        if (i <= n) out[i] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0 && total_out) *total_out = carry;
+}
+
 int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* partial, uint64_t* total_out,
                     cudaStream_t st) {
+    if (n <= 16384) {
+        scan_small_kernel<<<1, 1024, 0, st>>>(in, n, out, total_out);
+        return 1;
+    }
     // n+1 outputs: size the grid on n+1 so the last entry is always written
     const uint64_t nblocks = scan_blocks(n + 1);
     scan_block_sums_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(in, n, partial);

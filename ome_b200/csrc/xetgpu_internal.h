@@ -18,7 +18,10 @@ constexpr int kGearCap = 128;     // staged candidates per tile (fast path; expe
 
 // ---- K2 geometry.  Boundary resolution speculates per segment of kSegBytes (>= kMaxChunk, so every
 // full segment holds at least one cut); a segment holds at most kSegBytes/kMinChunk + 1 cuts.
-constexpr uint64_t kSegBytes = 2ull << 20;
+#ifndef XG_SEG_KIB
+#define XG_SEG_KIB 2048
+#endif
+constexpr uint64_t kSegBytes = (uint64_t)XG_SEG_KIB << 10;
 constexpr uint32_t kSegCap = (uint32_t)(kSegBytes / kMinChunk) + 2;
 
 // ---- K3 geometry.  A "group" is up to kLeavesPerGroup consecutive 1 KiB BLAKE3 leaves of one
