@@ -189,6 +189,17 @@ XetError* xetgpu_verify_file(XetGpuContext* ctx, const char* path, const char* e
 XetError* xetgpu_verify_buffer(XetGpuContext* ctx, const void* data, uint64_t len, int32_t memory,
                                const char* expected_hex);
 
+/*
+ * Verify a whole downloaded snapshot in one call: n files, each against its advertised hash
+ * (the list the Hub's tree API returns, HfTreeItem.xet_hash [pkg/xet/src/hf_adapter.rs:36-44]).
+ * All files are read and hashed as one batch.  out_ok (optional, n bytes) receives 1/0 per file.
+ * NULL when every file matches; otherwise code 6 with the mismatching paths and both hashes in
+ * `details` (one per line).  An entry of expected_hex may be NULL or "" to skip that file
+ * (files the Hub does not store through Xet carry no xet hash).
+ */
+XetError* xetgpu_verify_files(XetGpuContext* ctx, const char* const* paths, const char* const* expected_hex,
+                              size_t n_files, const XetCancellationToken* cancel_token, uint8_t* out_ok);
+
 /* MerkleHash::hex / MerkleHash::from_hex [used at pkg/xet/src/xet_downloader.rs:124-126]. */
 void xetgpu_hash_to_hex(const uint8_t hash[32], char out_hex[65]);
 XetError* xetgpu_hash_from_hex(const char* hex, uint8_t out_hash[32]);

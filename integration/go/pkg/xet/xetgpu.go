@@ -159,6 +159,45 @@ func (h *GpuHasher) VerifyFile(path, expectedHex string) error {
 	return convertGpuError(C.xetgpu_verify_file(h.ctx, cp, ce))
 }
 
+// VerifyFiles verifies a downloaded snapshot in one batch (paths[i] against expectedHex[i]; an empty
+// expected hash skips the file).  It returns the per-file verdicts; err is a *XetError with
+// Code == ErrorCodeChecksumMismatch when any file differs.
+func (h *GpuHasher) VerifyFiles(ctx context.Context, paths, expectedHex []string) ([]bool, error) {
+	n := len(paths)
+	if n == 0 {
+		return nil, nil
+	}
+	cp := make([]*C.char, n)
+	ch := make([]*C.char, n)
+	for i := range paths {
+		cp[i] = C.CString(paths[i])
+		if expectedHex[i] != "" {
+			ch[i] = C.CString(expectedHex[i])
+		}
+	}
+	defer func() {
+		for i := range cp {
+			C.free(unsafe.Pointer(cp[i]))
+			if ch[i] != nil {
+				C.free(unsafe.Pointer(ch[i]))
+			}
+		}
+	}()
+	handle := cgo.NewHandle(ctx)
+	defer handle.Delete()
+	tok := C.XetCancellationToken{
+		callback:  (C.XetCancellationCallback)(C.goXetShouldCancel),
+		user_data: unsafe.Pointer(handle),
+	}
+	ok := make([]C.uint8_t, n)
+	err := convertGpuError(C.xetgpu_verify_files(h.ctx, &cp[0], &ch[0], C.size_t(n), &tok, &ok[0]))
+	out := make([]bool, n)
+	for i := range ok {
+		out[i] = ok[i] != 0
+	}
+	return out, err
+}
+
 // IsChecksumMismatch reports whether err is a hash mismatch from VerifyFile.
 func IsChecksumMismatch(err error) bool {
 	var xe *XetError

@@ -66,6 +66,8 @@ SIGNATURES = {
     "xetgpu_hash_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.c_size_t, C.c_uint32,
                                  C.POINTER(XetCancellationToken), C.POINTER(C.POINTER(XetGpuResult))]),
     "xetgpu_verify_file": (ERRP, [CTX, C.c_char_p, C.c_char_p]),
+    "xetgpu_verify_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.c_size_t,
+                                   C.POINTER(XetCancellationToken), C.POINTER(C.c_uint8)]),
     "xetgpu_verify_buffer": (ERRP, [CTX, C.c_void_p, C.c_uint64, C.c_int32, C.c_char_p]),
     "xetgpu_hash_to_hex": (None, [C.POINTER(C.c_uint8), C.c_char_p]),
     "xetgpu_hash_from_hex": (ERRP, [C.c_char_p, C.POINTER(C.c_uint8)]),

@@ -1154,6 +1154,38 @@ extern "C" XetError* xetgpu_verify_file(XetGpuContext* c, const char* path, cons
     return e;
 }
 
+extern "C" XetError* xetgpu_verify_files(XetGpuContext* c, const char* const* paths, const char* const* expected_hex,
+                                         size_t n_files, const XetCancellationToken* cancel, uint8_t* out_ok) {
+    if (!c || (n_files && (!paths || !expected_hex)))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_verify_files");
+    std::vector<std::vector<uint8_t>> want(n_files);
+    for (size_t f = 0; f < n_files; f++) {
+        if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
+        if (expected_hex[f] && expected_hex[f][0]) {
+            want[f].resize(32);
+            if (XetError* e = xetgpu_hash_from_hex(expected_hex[f], want[f].data())) return e;
+        }
+    }
+    XetGpuResult* r = nullptr;
+    if (XetError* e = xetgpu_hash_files(c, paths, n_files, 0, cancel, &r)) return e;
+    std::string bad;
+    size_t n_bad = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        const bool ok = want[f].empty() || memcmp(r->files[f].file_hash, want[f].data(), 32) == 0;
+        if (out_ok) out_ok[f] = ok ? 1 : 0;
+        if (!ok) {
+            char hex[65];
+            xetgpu_hash_to_hex(r->files[f].file_hash, hex);
+            if (n_bad < 16) bad += std::string(paths[f]) + ": expected " + expected_hex[f] + " computed " + hex + "\n";
+            n_bad++;
+        }
+    }
+    xetgpu_free_result(r);
+    if (!n_bad) return nullptr;
+    return make_error(XETGPU_ERR_CHECKSUM_MISMATCH,
+                      "xet hash mismatch for " + std::to_string(n_bad) + " of " + std::to_string(n_files) + " files", bad);
+}
+
 extern "C" XetError* xetgpu_verify_buffer(XetGpuContext* c, const void* data, uint64_t len, int32_t memory,
                                           const char* expected_hex) {
     if (!c || !expected_hex || (len && !data))

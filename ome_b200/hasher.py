@@ -223,6 +223,18 @@ class XetHasher:
     def verify_file(self, path: str, expected_hex: str) -> None:
         _check(self._lib.xetgpu_verify_file(self._ctx, path.encode(), expected_hex.encode()))
 
+    def verify_files(self, paths: Sequence[str], expected_hex: Sequence[Optional[str]]) -> list:
+        """Verify a snapshot in one batch.  Returns the per-file ok flags; raises XetGpuError(code 6)
+        listing the mismatches when any file differs.  None / "" skips a file."""
+        n = len(paths)
+        assert len(expected_hex) == n
+        cp = (C.c_char_p * n)(*[p.encode() for p in paths])
+        ch = (C.c_char_p * n)(*[(h.encode() if h else None) for h in expected_hex])
+        ok = (C.c_uint8 * max(n, 1))()
+        self._last_ok = ok
+        _check(self._lib.xetgpu_verify_files(self._ctx, cp, ch, n, None, ok))
+        return [bool(ok[i]) for i in range(n)]
+
     def verify_buffer(self, data, expected_hex: str, memory: int = MEM_AUTO) -> None:
         addr, n, keep = _ptr_of(data)
         _check(self._lib.xetgpu_verify_buffer(self._ctx, addr, n, memory, expected_hex.encode()))

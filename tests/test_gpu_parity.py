@@ -227,6 +227,14 @@ def test_hash_files_and_verify(hasher, tmp_path):
         hasher.verify_buffer(datas[0], "xyz")
     assert ei.value.code == 1                                           # InvalidConfig
     hasher.verify_buffer(datas[0], cl.files[0].hex)
+    # snapshot verification in one batch: all good / one skipped / one wrong
+    good = [f.hex for f in cl.files]
+    assert hasher.verify_files(paths, good) == [True] * len(paths)
+    assert hasher.verify_files(paths, [good[0], None, "", good[3]]) == [True] * len(paths)
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.verify_files(paths, [good[0], good[1], bad, good[3]])
+    assert ei.value.code == 6 and "1 of 4" in ei.value.message and paths[2] in ei.value.details
+    assert [bool(x) for x in hasher._last_ok][:4] == [True, True, False, True]
     # small batches force several device round trips
     small = ome_b200.XetHasher(staging_bytes=1 << 20, max_batch_bytes=1 << 20)
     cl2 = small.hash_files(paths, want_chunks=True)
