@@ -211,6 +211,24 @@ def run_reference(args):
     }))
 
 
+def bind_to_gpu_numa(device_index: int):
+    """Best effort: run this rank on the CPU cores NVML reports as local to its GPU, so that the pinned
+    host shards (first-touch) and the copy threads sit on the GPU's NUMA node.  Returns the core count."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cores = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        cores = [c for c in cores if c in os.sched_getaffinity(0)]
+        if cores:
+            os.sched_setaffinity(0, cores)
+            return len(cores)
+    except Exception:
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------- GPU side
 def main():
     ap = argparse.ArgumentParser()
@@ -238,6 +256,7 @@ def main():
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local_rank)
+    numa_cores = bind_to_gpu_numa(local_rank) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -420,6 +439,7 @@ def main():
                                    + ("" if args.scale == 1.0 else f" (SCALED x{args.scale}: not the named config)"),
                        "shard_bytes": sizes, "bytes_per_gpu": total, "chunks_per_gpu": n_chunks,
                        "partition": "by file, one shard set per GPU" if world > 1 else "single GPU",
+                       "cpu_affinity": f"each rank bound to the {numa_cores} cores NVML reports local to its GPU" if numa_cores else None,
                        "l2": "inputs (16 GB) larger than L2 (126 MB); no explicit flush"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "parity": parity,
