@@ -238,8 +238,8 @@ XetError* xetgpu_range_exit_cut(XetGpuContext* ctx, const void* data, int32_t me
                                 uint64_t range_begin, uint64_t range_end, uint64_t entry_cut,
                                 uint64_t* out_exit_cut);
 
-/* K4 only: merkle root + file hash of a host list of (hash, size) pairs, on the GPU
- * (merklehash::aggregated_node_hash / file_hash). */
+/* K4 only: merkle root + file hash of a list of (hash, size) pairs, on the GPU
+ * (merklehash::aggregated_node_hash / file_hash).  The two input arrays may be host or device memory. */
 XetError* xetgpu_merkle_from_chunks(XetGpuContext* ctx, const uint8_t* chunk_hashes,
                                     const uint64_t* chunk_sizes, uint64_t n_chunks,
                                     uint8_t out_merkle_root[32], uint8_t out_file_hash[32]);

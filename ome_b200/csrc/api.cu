@@ -1312,10 +1312,11 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
     CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, 16, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(b.file_count, &cnt, 4, cudaMemcpyHostToDevice, st));
     if (n_chunks) {
-        CU(cudaMemcpyAsync(b.chunk_hash, chunk_hashes, n_chunks * 32, cudaMemcpyHostToDevice, st));
+        // cudaMemcpyDefault: the lists may live in host memory or (rank-0 combine of a sharded file) on the device
+        CU(cudaMemcpyAsync(b.chunk_hash, chunk_hashes, n_chunks * 32, cudaMemcpyDefault, st));
         // sizes may exceed 32 bits here (callers combine arbitrary (hash, size) lists): upload u64
         // sizes straight into the level-0 size array and skip the u32 chunk_len initialisation
-        CU(cudaMemcpyAsync(b.node_size[0], chunk_sizes, n_chunks * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b.node_size[0], chunk_sizes, n_chunks * 8, cudaMemcpyDefault, st));
     }
     CU(cudaStreamSynchronize(st));  // the host sources above are pageable stack/heap memory
     PipelineBuffers m = b;

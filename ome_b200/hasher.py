@@ -271,13 +271,22 @@ class XetHasher:
         del keep
         return exit_cut.value
 
-    def merkle_from_chunks(self, chunk_hashes: np.ndarray, chunk_sizes: np.ndarray):
-        h = np.ascontiguousarray(chunk_hashes, dtype=np.uint8).reshape(-1)
-        s = np.ascontiguousarray(chunk_sizes, dtype=np.uint64)
+    def merkle_from_chunks(self, chunk_hashes, chunk_sizes):
+        """(merkle root, file hash) of a chunk list: numpy arrays, or torch tensors on the host or the device
+        (uint8 [n, 32] and int64/uint64 [n])."""
         root = (C.c_uint8 * 32)()
         fh = (C.c_uint8 * 32)()
-        _check(self._lib.xetgpu_merkle_from_chunks(self._ctx, h.ctypes.data_as(C.POINTER(C.c_uint8)),
-                                                   s.ctypes.data_as(C.POINTER(C.c_uint64)), s.size, root, fh))
+        if hasattr(chunk_hashes, "data_ptr"):
+            h, s = chunk_hashes.contiguous(), chunk_sizes.contiguous()
+            assert h.element_size() == 1 and s.element_size() == 8 and h.numel() == 32 * s.numel()
+            hp = C.cast(h.data_ptr(), C.POINTER(C.c_uint8))
+            sp = C.cast(s.data_ptr(), C.POINTER(C.c_uint64))
+            n = s.numel()
+        else:
+            h = np.ascontiguousarray(chunk_hashes, dtype=np.uint8).reshape(-1)
+            s = np.ascontiguousarray(chunk_sizes, dtype=np.uint64)
+            hp, sp, n = h.ctypes.data_as(C.POINTER(C.c_uint8)), s.ctypes.data_as(C.POINTER(C.c_uint64)), s.size
+        _check(self._lib.xetgpu_merkle_from_chunks(self._ctx, hp, sp, n, root, fh))
         return bytes(root), bytes(fh)
 
     def fill_splitmix(self, device_ptr: int, seed: int, byte_off: int, length: int) -> None:

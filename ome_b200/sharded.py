@@ -219,33 +219,35 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
         _send_int(int(exit_cut), rank + 1, dev, group)
     out = RangeOutcome(ends, hashes, int(exit_cut), rehashed)
     _mark("carry_chain_ms")
-    # 4. chunk lists to rank 0
+    # 4. chunk lists to rank 0: one packed record array per rank (8-byte end + 32-byte hash), kept on the
+    #    communication device so that rank 0 can hand the concatenation straight to the merkle combine
     counts = torch.zeros(world, dtype=torch.int64, device=dev)
     counts[rank] = ends.size
     dist.all_reduce(counts, group=group)
     counts = counts.cpu().numpy()
-    mine_e = torch.from_numpy(np.ascontiguousarray(ends).astype(np.int64)).to(dev)
-    mine_h = torch.from_numpy(np.ascontiguousarray(hashes).reshape(-1).copy()).to(dev)
+
+    def pack(e, h):
+        rec = np.empty((e.size, 40), dtype=np.uint8)
+        rec[:, :8] = np.ascontiguousarray(e, dtype="<u8").view(np.uint8).reshape(-1, 8)
+        rec[:, 8:] = h
+        return torch.from_numpy(rec).to(dev)
+
     if rank == 0:
-        all_e, all_h = [ends.astype(np.uint64)], [hashes]
+        recs = [pack(ends, hashes)]
         for r in range(1, world):
-            n = int(counts[r])
-            e = torch.zeros(n, dtype=torch.int64, device=dev)
-            h = torch.zeros(n * 32, dtype=torch.uint8, device=dev)
-            if n:
-                dist.recv(e, _peer(r, group), group=group)
-                dist.recv(h, _peer(r, group), group=group)
-            all_e.append(e.cpu().numpy().astype(np.uint64))
-            all_h.append(h.cpu().numpy().reshape(n, 32))
-        e = np.concatenate(all_e)
-        h = np.concatenate(all_h)
-        sizes = np.diff(np.concatenate([[0], e])).astype(np.uint64)
+            t = torch.empty(int(counts[r]), 40, dtype=torch.uint8, device=dev)
+            if counts[r]:
+                dist.recv(t, _peer(r, group), group=group)
+            recs.append(t)
+        rec = torch.cat(recs)
+        e = rec[:, :8].contiguous().view(torch.int64).reshape(-1)
+        h = rec[:, 8:].contiguous()
+        sizes = torch.diff(e, prepend=torch.zeros(1, dtype=torch.int64, device=e.device))
         _mark("gather_ms")
         out.merkle_root, out.file_hash = engine.merkle_from_chunks(h, sizes)
-        out.n_chunks_total = int(e.size)
+        out.n_chunks_total = int(e.numel())
         _mark("merkle_ms")
     elif ends.size:
-        dist.send(mine_e, _peer(0, group), group=group)
-        dist.send(mine_h, _peer(0, group), group=group)
+        dist.send(pack(ends, hashes), _peer(0, group), group=group)
         _mark("gather_ms")
     return out

@@ -50,6 +50,8 @@ class OracleEngine:
         return _List(files)
 
     def merkle_from_chunks(self, hashes, sizes):
+        if hasattr(hashes, "numpy"):
+            hashes, sizes = hashes.cpu().numpy().reshape(-1, 32), sizes.cpu().numpy().astype(np.uint64)
         return xet_oracle.merkle_root(hashes, sizes) if len(sizes) else bytes(32), \
             xet_oracle.file_hash_from_chunks(hashes, sizes)
 
