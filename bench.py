@@ -415,17 +415,22 @@ def main():
         # input byte read once = the rank's total bytes (DESIGN.md "Roofline").
         leaf_ms = stage["leaf_kernel_ms"] / args.steps
         achieved = total / (leaf_ms / 1e3) / 1e9 if leaf_ms > 0 else None
-        traffic, traffic_src = None, None
+        traffic, traffic_src, pipes = None, None, None
         ncu_path = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
         if os.path.exists(ncu_path):  # DRAM bytes per algorithmic byte of this kernel, from the committed ncu --set full capture
-            ratio = json.load(open(ncu_path)).get("leaf_group_kernel_traffic_per_algorithmic_byte")
+            ncu = json.load(open(ncu_path))
+            ratio = ncu.get("leaf_group_kernel_traffic_per_algorithmic_byte")
             if ratio:
                 traffic = round(ratio * total / 1e9, 3)
                 traffic_src = f"profiles/r1_ncu_summary.json: (dram read + write) / algorithmic bytes = {ratio} on a 2 GiB launch, scaled to this launch; GB"
+            k = ncu.get("kernels", {}).get("leaf_group_kernel", {})
+            pipes = {"source": "ncu --set full (profiles/r1_ncu_summary.json), not measured in this run",
+                     "alu_pipe_pct_of_peak": k.get("alu_pct"), "fma_pipe_pct_of_peak": k.get("fma_pct"),
+                     "issue_slots_pct": k.get("issue_pct"), "dram_pct_of_peak": k.get("dram_pct")}
         roofline = {"bound": "hbm", "kernel": "leaf_group_kernel", "achieved": round(achieved, 1) if achieved else None,
                     "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4) if achieved else None,
                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": total,
+                    "algorithmic_bytes_per_launch": total, "binding_resource": pipes,
                     "note": "ALU-issue bound, not HBM bound: ncu shows the ALU pipe 89 % busy at 24 % DRAM throughput "
                             "(profiles/r1_summary.md); ~15 lane-instructions per byte of keyed BLAKE3",
                     "per_stage_ms": {k: round(v / args.steps, 4) for k, v in stage.items()},
