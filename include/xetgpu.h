@@ -89,8 +89,9 @@ typedef struct XetGpuContext XetGpuContext; /* opaque; one per (process, GPU) */
 typedef struct {
     int32_t device;             /* CUDA device ordinal; -1 = current device */
     void* stream;               /* cudaStream_t to launch on; NULL = a stream the context owns */
-    uint64_t staging_bytes;     /* size of EACH of the two pinned host staging buffers used for
-                                   host->device ingestion; 0 = 64 MiB */
+    uint64_t staging_bytes;     /* size of EACH of the two pinned host staging buffers used to copy
+                                   pageable host memory; 0 = 64 MiB.  xetgpu_hash_files reads through a ring
+                                   of 16 pinned slots of min(staging_bytes, 64 MiB) each (16 MiB when 0) */
     uint64_t max_batch_bytes;   /* xetgpu_hash_files: bytes resident on the device per batch;
                                    0 = 8 GiB */
     uint32_t flags;             /* XETGPU_CTX_* */
