@@ -100,6 +100,8 @@ struct XetGpuContext {
         Arena ws;
         uint8_t* h_meta = nullptr;
         uint64_t h_meta_cap = 0;
+        uint8_t* h_chunks = nullptr;  // pinned bounce buffer for chunk-list readback (pageable D2H runs at ~2.5 GB/s)
+        uint64_t h_chunks_cap = 0;
         cudaEvent_t ev[8] = {};
         cudaEvent_t ev_kernel[4] = {};
     } lanes[2];
@@ -224,6 +226,7 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
         if (l.stream) cudaStreamSynchronize(l.stream);
         if (l.ws.base) cudaFree(l.ws.base);
         if (l.h_meta) cudaFreeHost(l.h_meta);
+        if (l.h_chunks) cudaFreeHost(l.h_chunks);
         for (auto& ev : l.ev)
             if (ev) cudaEventDestroy(ev);
         for (auto& ev : l.ev_kernel)
@@ -634,13 +637,25 @@ static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const
     if (opt.want_chunks && n_chunks) {
         rb->ends.resize(chunk0 + n_chunks);
         rb->hashes.resize((chunk0 + n_chunks) * 32);
+        if (n_chunks * 40 > lane->h_chunks_cap) {
+            if (lane->h_chunks) cudaFreeHost(lane->h_chunks);
+            lane->h_chunks = nullptr;
+            lane->h_chunks_cap = 0;
+            const uint64_t cap = n_chunks * 40 + n_chunks * 5 + 4096;
+            CU(cudaMallocHost((void**)&lane->h_chunks, cap));
+            lane->h_chunks_cap = cap;
+        }
+        uint8_t* pe = lane->h_chunks;
+        uint8_t* ph = lane->h_chunks + n_chunks * 8;
         if (opt.resolve_only) {  // ends only: gather was skipped; single file in this mode
-            CU(cudaMemcpyAsync(rb->ends.data() + chunk0, b.slot_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(pe, b.slot_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
         } else {
-            CU(cudaMemcpyAsync(rb->ends.data() + chunk0, b.out_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
-            CU(cudaMemcpyAsync(rb->hashes.data() + chunk0 * 32, b.out_hash, n_chunks * 32, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(pe, b.out_end, n_chunks * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(ph, b.out_hash, n_chunks * 32, cudaMemcpyDeviceToHost, st));
         }
         CU(cudaStreamSynchronize(st));
+        memcpy(rb->ends.data() + chunk0, pe, n_chunks * 8);
+        if (!opt.resolve_only) memcpy(rb->hashes.data() + chunk0 * 32, ph, n_chunks * 32);
         if (opt.end_bias)
             for (uint64_t i = 0; i < n_chunks; i++) rb->ends[chunk0 + i] += opt.end_bias;
     }
