@@ -72,6 +72,54 @@ def split_byte_ranges(file_len: int, world: int, align: int = 4096) -> List[Tupl
     return [(bounds[r], bounds[r + 1]) for r in range(world)]
 
 
+@dataclass
+class Piece:
+    file: int      # global file index
+    begin: int     # byte range of the file this rank owns
+    end: int
+    file_len: int
+
+    @property
+    def whole(self) -> bool:
+        return self.begin == 0 and self.end == self.file_len
+
+
+def plan_concatenated(file_sizes: Sequence[int], world: int, align: int = 4096) -> List[List[Piece]]:
+    """BASELINE config 4: the files laid end to end are cut into `world` equal byte ranges; a file that
+    straddles a range boundary is shared by consecutive ranks (byte-range protocol), every other file is
+    hashed whole by one rank.  A boundary that would leave a piece shorter than RANGE_LEAD + align at either
+    end of a file snaps to that end, and in-file boundaries are aligned down to `align`.
+    Returns, per rank, its pieces in file order; every file's pieces are consecutive ranks' and tile it."""
+    total = sum(file_sizes)
+    starts = np.concatenate([[0], np.cumsum(file_sizes)]).astype(np.int64)
+    min_piece = RANGE_LEAD + align
+    cuts = [0]                                    # positions in the concatenated space
+    for r in range(1, world):
+        pos = total * r // world
+        f = int(np.searchsorted(starts, pos, side="right") - 1)
+        f = min(max(f, 0), len(file_sizes) - 1)
+        off = (pos - int(starts[f])) // align * align
+        if off < min_piece:
+            off = 0
+        elif file_sizes[f] - off < min_piece:
+            off = file_sizes[f]
+        cuts.append(max(int(starts[f]) + off, cuts[-1]))
+    cuts.append(total)
+    plan: List[List[Piece]] = [[] for _ in range(world)]
+    for r in range(world):
+        lo, hi = cuts[r], cuts[r + 1]
+        for f, n in enumerate(file_sizes):
+            fb, fe = int(starts[f]), int(starts[f]) + n
+            if n == 0:
+                if lo <= fb < hi or (r == world - 1 and fb == total):   # an empty file belongs to one rank
+                    plan[r].append(Piece(f, 0, 0, 0))
+                continue
+            b, e = max(lo, fb), min(hi, fe)
+            if b < e:
+                plan[r].append(Piece(f, b - fb, e - fb, n))
+    return plan
+
+
 # ------------------------------------------------------------------------------- file partition
 def hash_files_partitioned(engine, local_files: Sequence[Tuple[int, object]], n_files: int,
                            group=None, comm_device: Optional[torch.device] = None):

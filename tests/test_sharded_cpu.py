@@ -131,3 +131,29 @@ def test_fixup_window_is_small_on_random_data():
     begin, end = out[1]["range"]
     assert 0 < out[1]["rehashed"] <= sharded.FIX_WINDOW + sharded.RANGE_LEAD < end - begin
     assert len(out[1]["calls"]) == 2                        # speculative pass + one fix-up window
+
+
+def test_plan_concatenated_tiles_every_file():
+    rng = np.random.default_rng(4)
+    for world in (1, 2, 3, 8):
+        for sizes in ([4_230_000_000] * 163, [5, 0, 300_000, 0, 7_000_000, 1_000_000, 0],
+                      [int(x) for x in rng.integers(0, 3_000_000, 40)], [0, 0], [10_000_000]):
+            plan = sharded.plan_concatenated(sizes, world)
+            assert len(plan) == world
+            owned = {f: [] for f in range(len(sizes))}
+            for r, pieces in enumerate(plan):
+                assert [p.file for p in pieces] == sorted(p.file for p in pieces)
+                for p in pieces:
+                    owned[p.file].append((r, p.begin, p.end))
+                    assert p.file_len == sizes[p.file]
+            for f, n in enumerate(sizes):
+                ps = owned[f]
+                assert ps, (world, f)                                  # every file, empty ones too, has an owner
+                assert ps[0][1] == 0 and ps[-1][2] == n
+                assert all(ps[i][2] == ps[i + 1][1] and ps[i + 1][0] == ps[i][0] + 1 for i in range(len(ps) - 1))
+                if len(ps) > 1:                                        # shared files: every piece can feed a halo
+                    assert all(e - b >= sharded.RANGE_LEAD for _, b, e in ps)
+            if sum(sizes) > 10 * world * (sharded.RANGE_LEAD + 4096):  # balanced to within one file-end snap
+                loads = [sum(p.end - p.begin for p in pieces) for pieces in plan]
+                assert max(loads) - min(loads) <= 2 * (sharded.RANGE_LEAD + 4096) + max(sizes) * 0 + 4096 * world \
+                    or max(sizes) < sum(sizes) // world
