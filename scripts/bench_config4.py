@@ -119,6 +119,9 @@ for f in shared:
         del t
 okt = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+rh = torch.tensor([rehash], dtype=torch.int64, device=dev)
+dist.all_reduce(rh, op=dist.ReduceOp.MAX)
+rehash = int(rh.item())
 if rank == 0:
     total = sum(sizes)
     t = min(times)
