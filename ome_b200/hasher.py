@@ -72,9 +72,41 @@ class FileHash:
         return hash_to_hex(self.file_hash)
 
 
+_FILE_DTYPE = np.dtype([("file_hash", "u1", 32), ("merkle_root", "u1", 32), ("size", "<u8"), ("n_chunks", "<u8"),
+                        ("first_chunk", "<u8")])
+assert _FILE_DTYPE.itemsize == C.sizeof(L.XetGpuFileResult)
+
+
+class FileList:
+    """Per-file results of one call: a read-only sequence of FileHash built on demand from one copied
+    record array (a batch of 200,000 small files should not cost 200,000 Python objects up front)."""
+
+    def __init__(self, records: np.ndarray):
+        self.records = records
+
+    def __len__(self) -> int:
+        return int(self.records.shape[0])
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        r = self.records[i]
+        return FileHash(r["file_hash"].tobytes(), r["merkle_root"].tobytes(), int(r["size"]), int(r["n_chunks"]),
+                        int(r["first_chunk"]))
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+    def __eq__(self, other):
+        return list(self) == list(other)
+
+    def __repr__(self):
+        return f"FileList({len(self)} files)"
+
+
 @dataclass
 class ChunkList:
-    files: list                      # [FileHash]
+    files: FileList                  # sequence of FileHash
     chunk_ends: Optional[np.ndarray]    # uint64 [n_chunks], file-relative exclusive ends
     chunk_hashes: Optional[np.ndarray]  # uint8 [n_chunks, 32]
 
@@ -171,10 +203,11 @@ class XetHasher:
     # -- results
     def _take(self, resp, want_chunks: bool) -> ChunkList:
         r = resp.contents
-        files = []
-        for i in range(r.n_files):
-            f = r.files[i]
-            files.append(FileHash(bytes(f.file_hash), bytes(f.merkle_root), f.size, f.n_chunks, f.first_chunk))
+        if r.n_files:
+            raw = C.string_at(r.files, r.n_files * _FILE_DTYPE.itemsize)
+            files = FileList(np.frombuffer(raw, dtype=_FILE_DTYPE))
+        else:
+            files = FileList(np.zeros(0, dtype=_FILE_DTYPE))
         ends = hashes = None
         if want_chunks:
             n = r.n_chunks
