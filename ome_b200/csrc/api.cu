@@ -434,6 +434,121 @@ static XetError* ensure_workspace(Lane* l, const Plan& p, PipelineBuffers* b) {
 // Copy host bytes to the device through the two pinned staging buffers: the CPU fills one buffer
 // while the DMA engine drains the other.  Pinned callers (cudaHostAlloc / cudaHostRegister) are
 // copied directly in staging-sized pieces.
+// File ingestion.  A single read() loop moves ~5 GB/s out of the page cache — no faster than the CPU
+// reference hashes — so a batch is cut into pieces that a small pool of reader threads pread() into a
+// ring of pinned slots; the thread that filled a slot enqueues its host->device copy itself (the
+// copies land in disjoint device ranges, so their order on the stream does not matter) and the slot
+// is reused once that copy's event has fired.
+struct ReadPiece {
+    int fd;               // file to pread() from, or -1 ...
+    const uint8_t* mem;   // ... for a piece of (pageable) host memory to memcpy
+    uint64_t file_off, len, dev_off;
+    size_t file;          // index into paths (for error text)
+};
+
+struct ReaderPool {
+    XetGpuContext* c = nullptr;
+    cudaStream_t stream = nullptr;   // stream the host->device copies are enqueued on
+    uint8_t* d_base = nullptr;       // device destination of dev_off 0
+    const char* const* paths = nullptr;
+    std::vector<ReadPiece> pieces;
+    std::vector<uint8_t*> slots;
+    std::vector<cudaEvent_t> slot_ev;
+    std::vector<long> slot_issued;  // index of the last piece whose copy was enqueued from this slot (-1: none)
+    std::mutex mu;
+    std::condition_variable cv;
+    std::atomic<size_t> next{0};
+    std::atomic<uint64_t> bytes_done{0};
+    std::atomic<bool> stop{false};
+    XetError* err = nullptr;
+
+    void fail(XetError* e) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!err) err = e;
+        else xetgpu_free_error(e);
+        stop = true;
+        cv.notify_all();
+    }
+
+    void worker() {
+        cudaSetDevice(c->device);
+        const size_t S = slots.size();
+        while (!stop) {
+            const size_t i = next.fetch_add(1);
+            if (i >= pieces.size()) return;
+            const size_t s = i % S;
+            {   // the slot is free once the piece that used it last (i - S) has enqueued its copy ...
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || slot_issued[s] == (long)i - (long)S; });
+                if (stop) return;
+            }
+            cudaEventSynchronize(slot_ev[s]);  // ... and the last copy out of this slot (any stream, any call) has drained
+            const ReadPiece& p = pieces[i];
+            uint64_t got = 0;
+            if (p.fd < 0) {
+                memcpy(slots[s], p.mem, p.len);
+                got = p.len;
+            }
+            while (got < p.len) {
+                ssize_t r = pread(p.fd, slots[s] + got, p.len - got, (off_t)(p.file_off + got));
+                if (r < 0 && errno == EINTR) continue;
+                if (r <= 0) {
+                    fail(make_error(XETGPU_ERR_IO, r < 0 ? std::string("read failed: ") + strerror(errno)
+                                                          : std::string("file shrank while being read"),
+                                    paths ? paths[p.file] : ""));
+                    return;
+                }
+                got += (uint64_t)r;
+            }
+            cudaError_t ce = cudaMemcpyAsync(d_base + p.dev_off, slots[s], p.len, cudaMemcpyHostToDevice, stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(slot_ev[s], stream);
+            if (ce != cudaSuccess) {
+                fail(cuda_error(ce, "cudaMemcpyAsync(H2D)"));
+                return;
+            }
+            bytes_done += p.len;
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                slot_issued[s] = (long)i;
+            }
+            cv.notify_all();
+        }
+    }
+};
+
+static XetError* ensure_read_slots(XetGpuContext* c) {
+    if (c->read_slots.size() == kReadSlots) return nullptr;
+    for (size_t i = c->read_slots.size(); i < kReadSlots; i++) {
+        uint8_t* p = nullptr;
+        CU(cudaMallocHost((void**)&p, c->read_slot_bytes));
+        cudaEvent_t ev;
+        CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        c->read_slots.push_back(p);
+        c->read_slot_ev.push_back(ev);
+    }
+    return nullptr;
+}
+
+// Runs the pool to completion (all copies enqueued); `poll` is called every few milliseconds on this thread.
+template <typename Poll>
+static XetError* run_reader_pool(XetGpuContext* c, ReaderPool& pool, Poll poll) {
+    if (pool.pieces.empty()) return nullptr;
+    pool.c = c;
+    pool.slots = c->read_slots;
+    pool.slot_ev = c->read_slot_ev;
+    pool.slot_issued.assign(kReadSlots, -1);
+    for (size_t s = 0; s < kReadSlots; s++) pool.slot_issued[s] = (long)s - (long)kReadSlots;
+    const size_t nthreads = std::min<size_t>(std::min<size_t>(c->read_threads, pool.pieces.size()), kReadSlots);
+    std::vector<std::thread> threads;
+    for (size_t t = 0; t < nthreads; t++) threads.emplace_back([&pool] { pool.worker(); });
+    while (pool.next.load() < pool.pieces.size() && !pool.stop) {
+        std::this_thread::sleep_for(std::chrono::milliseconds(2));
+        poll(pool);
+    }
+    for (auto& t : threads) t.join();
+    return pool.err;
+}
+
 static XetError* ensure_staging(XetGpuContext* c) {
     for (int i = 0; i < 2; i++)
         if (!c->h_stage[i]) CU(cudaMallocHost((void**)&c->h_stage[i], c->staging_bytes));
@@ -457,6 +572,15 @@ static XetError* ingest_host(XetGpuContext* c, cudaStream_t stream, const uint8_
             CU(cudaMemcpyAsync(d_dst + o, src + o, n, cudaMemcpyHostToDevice, stream));
         }
         return nullptr;
+    }
+    if (bytes > c->read_slot_bytes) {  // pageable memory: several threads copy into the pinned slot ring
+        if (XetError* e = ensure_read_slots(c)) return e;
+        ReaderPool pool;
+        pool.stream = stream;
+        pool.d_base = d_dst;
+        for (uint64_t o = 0; o < bytes; o += c->read_slot_bytes)
+            pool.pieces.push_back(ReadPiece{-1, src + o, 0, std::min<uint64_t>(c->read_slot_bytes, bytes - o), o, 0});
+        return run_reader_pool(c, pool, [](ReaderPool&) {});
     }
     if (XetError* e = ensure_staging(c)) return e;
     int i = 0;
@@ -936,94 +1060,6 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
 }
 
 // -------------------------------------------------------------------------------------- files
-// File ingestion.  A single read() loop moves ~5 GB/s out of the page cache — no faster than the CPU
-// reference hashes — so a batch is cut into pieces that a small pool of reader threads pread() into a
-// ring of pinned slots; the thread that filled a slot enqueues its host->device copy itself (the
-// copies land in disjoint device ranges, so their order on the stream does not matter) and the slot
-// is reused once that copy's event has fired.
-struct ReadPiece {
-    int fd;
-    uint64_t file_off, len, dev_off;
-    size_t file;  // index into paths (for error text)
-};
-
-struct ReaderPool {
-    XetGpuContext* c = nullptr;
-    const char* const* paths = nullptr;
-    std::vector<ReadPiece> pieces;
-    std::vector<uint8_t*> slots;
-    std::vector<cudaEvent_t> slot_ev;
-    std::vector<long> slot_issued;  // index of the last piece whose copy was enqueued from this slot (-1: none)
-    std::mutex mu;
-    std::condition_variable cv;
-    std::atomic<size_t> next{0};
-    std::atomic<uint64_t> bytes_done{0};
-    std::atomic<bool> stop{false};
-    XetError* err = nullptr;
-
-    void fail(XetError* e) {
-        std::lock_guard<std::mutex> lk(mu);
-        if (!err) err = e;
-        else xetgpu_free_error(e);
-        stop = true;
-        cv.notify_all();
-    }
-
-    void worker() {
-        cudaSetDevice(c->device);
-        const size_t S = slots.size();
-        while (!stop) {
-            const size_t i = next.fetch_add(1);
-            if (i >= pieces.size()) return;
-            const size_t s = i % S;
-            {   // the slot is free once the piece that used it last (i - S) has enqueued its copy ...
-                std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return stop || slot_issued[s] == (long)i - (long)S; });
-                if (stop) return;
-            }
-            if (i >= S) cudaEventSynchronize(slot_ev[s]);  // ... and that copy has drained
-            const ReadPiece& p = pieces[i];
-            uint64_t got = 0;
-            while (got < p.len) {
-                ssize_t r = pread(p.fd, slots[s] + got, p.len - got, (off_t)(p.file_off + got));
-                if (r < 0 && errno == EINTR) continue;
-                if (r <= 0) {
-                    fail(make_error(XETGPU_ERR_IO, r < 0 ? std::string("read failed: ") + strerror(errno)
-                                                          : std::string("file shrank while being read"),
-                                    paths[p.file]));
-                    return;
-                }
-                got += (uint64_t)r;
-            }
-            cudaError_t ce = cudaMemcpyAsync(c->d_input + p.dev_off, slots[s], p.len, cudaMemcpyHostToDevice, c->stream);
-            if (ce == cudaSuccess) ce = cudaEventRecord(slot_ev[s], c->stream);
-            if (ce != cudaSuccess) {
-                fail(cuda_error(ce, "cudaMemcpyAsync(H2D)"));
-                return;
-            }
-            bytes_done += p.len;
-            {
-                std::lock_guard<std::mutex> lk(mu);
-                slot_issued[s] = (long)i;
-            }
-            cv.notify_all();
-        }
-    }
-};
-
-static XetError* ensure_read_slots(XetGpuContext* c) {
-    if (c->read_slots.size() == kReadSlots) return nullptr;
-    for (size_t i = c->read_slots.size(); i < kReadSlots; i++) {
-        uint8_t* p = nullptr;
-        CU(cudaMallocHost((void**)&p, c->read_slot_bytes));
-        cudaEvent_t ev;
-        CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        c->read_slots.push_back(p);
-        c->read_slot_ev.push_back(ev);
-    }
-    return nullptr;
-}
-
 extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* paths, size_t n_files, uint32_t flags,
                                        const XetCancellationToken* cancel, XetGpuResult** out_result) {
     if (!c || !out_result || (n_files && !paths))
@@ -1069,12 +1105,9 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
         }
         std::vector<uint64_t> rel(f1 - f0 + 1, 0);
         ReaderPool pool;
-        pool.c = c;
         pool.paths = paths;
-        pool.slots = c->read_slots;
-        pool.slot_ev = c->read_slot_ev;
-        pool.slot_issued.assign(kReadSlots, -1);
-        for (size_t s = 0; s < kReadSlots; s++) pool.slot_issued[s] = (long)s - (long)kReadSlots;
+        pool.stream = c->stream;
+        pool.d_base = c->d_input;
         std::vector<int> fds;
         uint64_t dev_off = 0;
         for (size_t f = f0; f < f1; f++) {
@@ -1087,25 +1120,18 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
             }
             if (fd >= 0) fds.push_back(fd);
             for (uint64_t o = 0; o < sizes[f]; o += c->read_slot_bytes)
-                pool.pieces.push_back(ReadPiece{fd, o, std::min<uint64_t>(c->read_slot_bytes, sizes[f] - o), dev_off + o, f});
+                pool.pieces.push_back(
+                    ReadPiece{fd, nullptr, o, std::min<uint64_t>(c->read_slot_bytes, sizes[f] - o), dev_off + o, f});
             dev_off += sizes[f];
         }
         rel[f1 - f0] = dev_off;
-        if (!err && !pool.pieces.empty()) {
-            const size_t nthreads = std::min<size_t>(std::min<size_t>(c->read_threads, pool.pieces.size()), kReadSlots);
-            std::vector<std::thread> threads;
-            for (size_t t = 0; t < nthreads; t++) threads.emplace_back([&pool] { pool.worker(); });
-            // this thread reports progress and polls for cancellation while the readers work
-            while (pool.next.load() < pool.pieces.size() && !pool.stop) {
-                std::this_thread::sleep_for(std::chrono::milliseconds(5));
-                pu.completed_bytes = bytes_before + pool.bytes_done.load();
+        if (!err)  // this thread reports progress and polls for cancellation while the readers work
+            err = run_reader_pool(c, pool, [&](ReaderPool& pl) {
+                pu.completed_bytes = bytes_before + pl.bytes_done.load();
                 report_progress(c, pu, false);
                 if (cancel && cancel->callback && cancel->callback(cancel->user_data))
-                    pool.fail(make_error(XETGPU_ERR_CANCELLED, "cancelled"));
-            }
-            for (auto& t : threads) t.join();
-            err = pool.err;
-        }
+                    pl.fail(make_error(XETGPU_ERR_CANCELLED, "cancelled"));
+            });
         for (int fd : fds) close(fd);
         if (err) break;
         bytes_before += bytes;
