@@ -107,6 +107,7 @@ struct XetGpuContext {
     } lanes[2];
     cudaEvent_t ev_fork = nullptr;
     cudaEvent_t ev_gear_done[2] = {nullptr, nullptr};
+    int force_lanes = -1;  // XETGPU_TWO_LANES=0/1 overrides the two-lane policy (experiments)
     uint64_t min_group_bytes = 256ull << 20;  // smallest file group worth its own lane (XETGPU_MIN_GROUP_BYTES)
     uint8_t* d_input = nullptr;  // device copy of host inputs
     uint64_t d_input_cap = 0;
@@ -194,6 +195,7 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
     }
     cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     for (auto& ev : c->ev_gear_done) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (const char* v = getenv("XETGPU_TWO_LANES")) c->force_lanes = atoi(v) ? 1 : 0;
     if (const char* v = getenv("XETGPU_MIN_GROUP_BYTES")) {  // test knob: exercise the two-lane path on small inputs
         unsigned long long n = strtoull(v, nullptr, 10);
         if (n) c->min_group_bytes = n;
@@ -898,7 +900,8 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
     // files (+8 % on 10,000 files: the short latency-bound kernels of one group hide behind the other group's
     // bulk kernels); a few large device-resident files run fastest as one group (the gear and BLAKE3 kernels
     // each fill the SMs' shared memory, so they cannot be co-resident anyway).
-    const bool two_lanes = !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && (host.base != nullptr || n_files >= 16);
+    bool two_lanes = !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && (host.base != nullptr || n_files >= 16);
+    if (c->force_lanes >= 0 && !opt.range) two_lanes = c->force_lanes == 1;
     if (two_lanes) {
         uint64_t acc = 0;
         for (size_t f = 0; f < n_files; f++) {
