@@ -429,3 +429,16 @@ def test_degenerate_batches(hasher):
     assert cl.files[1].n_chunks == 0 and cl.files[1].file_hash == bytes(32)
     check_against_oracle(cl, 2, d)
     assert hasher.gear_candidates(b"").size == 0
+
+
+def test_cpp_host_mirror(tmp_path):
+    """include/xetgpu.hpp (GpuHasher: HashFiles / HashBytes / VerifyFile / VerifyFiles, XetError) — the C++
+    stand-in for the Go wrappers, checked by tests/cpp/host_test.cpp against hf_xet golden values."""
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "tools", "xetgpu_host_test")
+    if not os.path.exists(exe):
+        pytest.skip("tools/xetgpu_host_test not built")
+    r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.startswith("ok")
