@@ -55,3 +55,20 @@ def test_product_code_never_touches_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".go")):
                 txt = open(os.path.join(dp, fn), errors="replace").read()
                 assert "xet_oracle" not in txt and "oracle/" not in txt, os.path.join(dp, fn)
+
+
+def test_cpp_consumers_fail_loudly_without_gpu(tmp_path):
+    """tools/xetsum (plain C ABI) and tools/xetgpu_host_test (include/xetgpu.hpp) build, link against the
+    library and, with no CUDA device, stop with the library's error instead of computing anything."""
+    import subprocess
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    p = tmp_path / "x.bin"
+    p.write_bytes(b"hello world")
+    for exe, args in (("xetsum", [str(p)]), ("xetgpu_host_test", [str(tmp_path)])):
+        path = os.path.join(ROOT, "tools", exe)
+        if not os.path.exists(path):
+            pytest.skip(f"tools/{exe} not built")
+        r = subprocess.run([path] + args, capture_output=True, text=True)
+        assert r.returncode == 2 and "no CUDA device" in r.stderr, (exe, r.stdout, r.stderr)
