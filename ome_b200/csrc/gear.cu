@@ -108,7 +108,42 @@ struct GearLane {
     uint32_t tab;     // shared-memory address of the table
     uint32_t lane8;   // lane * 8
     uint64_t h;       // rolling hash
+    uint32_t two;     // the constant 2, loaded from constant memory so that ptxas keeps the IMADs below
 };
+
+// h' = 2h + t (mod 2^64).  XG_GEAR_ROLL selects the pipe the roll issues on.  Measured on B200 (config 2, 16.06 GB,
+// profiles/r2_coresidency_variants.jsonl): 0 -> 4.20 ms, 1 -> 4.45 ms, 2 -> 4.63 ms for the kernel alone — the
+// IMAD.WIDE is a half-rate instruction, so moving the roll off the ALU pipe costs more issue slots than it
+// frees; mode 1 exists for builds in which an ALU-bound kernel shares the SM.
+//   0  ALU:  IADD3 + IADD3.X
+//   1  FMA:  IMAD.WIDE.U32 (low word * 2 + t, 64-bit result carries into the high word) + IMAD (high word * 2 + carry)
+//   2  split: IMAD.WIDE.U32 on the FMA pipe, high word as a 3-input add on the ALU pipe
+#ifndef XG_GEAR_ROLL
+#define XG_GEAR_ROLL 0
+#endif
+static __constant__ uint32_t c_gear_two = 2u;
+
+__device__ __forceinline__ uint64_t gear_roll(uint64_t h, uint64_t t, uint32_t two) {
+#if XG_GEAR_ROLL == 0
+    return (h << 1) + t;
+#else
+    const uint32_t hl = (uint32_t)h, hh = (uint32_t)(h >> 32);
+    // mad.lo.cc + madc.hi is the PTX form ptxas turns into ONE IMAD.WIDE.U32 with a 64-bit addend
+    // ({tl, th} + hl * 2: low word and th + carry); mad.wide.u32 with a 64-bit addend and the C expression are
+    // both split into IMAD.WIDE + extra ALU adds.
+    const uint32_t tl = (uint32_t)t, th = (uint32_t)(t >> 32);
+    uint32_t l, hc;
+    asm("mad.lo.cc.u32 %0, %2, %3, %4;\n\tmadc.hi.u32 %1, %2, %3, %5;" : "=r"(l), "=r"(hc) : "r"(hl), "r"(two), "r"(tl), "r"(th));
+    const uint64_t lo = ((uint64_t)hc << 32) | l;
+    uint32_t nh;
+#if XG_GEAR_ROLL == 1
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(nh) : "r"(hh), "r"(two), "r"(hc));
+#else
+    nh = hh + hh + hc;
+#endif
+    return ((uint64_t)nh << 32) | (uint32_t)lo;
+#endif
+}
 
 template <int J>
 __device__ __forceinline__ uint64_t gear_lookup(const GearLane& g, uint32_t w) {
@@ -132,7 +167,7 @@ __device__ __forceinline__ void gear_chunk16(GearLane& g, uint4 v, uint32_t base
     uint32_t lowest = 0xffffffffu;  // min over the 16 positions of the hash's high word: one ALU op per byte
 #pragma unroll
     for (int j = 0; j < 16; j++) {
-        h = (h << 1) + t[j];
+        h = gear_roll(h, t[j], g.two);
         if (kTest) lowest = min(lowest, (uint32_t)(h >> 32));
     }
     g.h = h;
@@ -140,7 +175,7 @@ __device__ __forceinline__ void gear_chunk16(GearLane& g, uint4 v, uint32_t base
         uint64_t r = h0;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-            r = (r << 1) + t[j];
+            r = gear_roll(r, t[j], g.two);
             if ((uint32_t)(r >> 32) < (1u << (32 - kTopBits))) on_match(base + j);
         }
     }
@@ -184,6 +219,7 @@ __global__ void __launch_bounds__(kGearThreads, 1)
     GearLane g;
     g.tab = smem_u32(s_table);
     g.lane8 = lane * 8u;
+    g.two = c_gear_two;
     auto emit = [&](uint32_t pos) {
         const uint32_t slot = atomicAdd(s_cnt, 1u);
         if (slot < kGearCap) s_list[slot] = pos;
