@@ -106,6 +106,11 @@ enum {
     XETGPU_MEM_HOST = 1,   /* host memory (pageable or pinned) */
     XETGPU_MEM_DEVICE = 2, /* device memory on the context's GPU, 16-byte aligned */
 };
+/* Stream-ordering rule for device inputs: the library reads them on the context's stream (XetGpuConfig.stream, or
+ * a non-blocking stream of its own, which takes no implicit ordering from the legacy default stream or from any
+ * other stream).  The bytes must therefore be COMPLETE with respect to that stream when the call is made: either
+ * create the context on the stream that produces them, or synchronise the producing stream first.  The Python
+ * binding does the latter for torch tensors (ome_b200/hasher.py, _order_after_torch). */
 
 #define XETGPU_WANT_CHUNKS 1u /* also return per-chunk end offsets and hashes */
 

@@ -165,6 +165,7 @@ class XetHasher:
         _check(self._lib.xetgpu_context_new(C.byref(cfg), C.byref(ctx)))
         self._ctx = ctx
         self._cb = None
+        self._stream = int(stream or 0)
 
     # -- lifecycle (Close in pkg/xet/xet.go:288-308)
     def close(self) -> None:
@@ -200,6 +201,17 @@ class XetHasher:
         self._cb = L.ProgressCallback(bridge)
         _check(self._lib.xetgpu_context_set_progress_callback(self._ctx, self._cb, None, throttle_ms))
 
+    def _order_after_torch(self, data) -> None:
+        """Device inputs must be complete with respect to the context's stream (include/xetgpu.h, XETGPU_MEM_DEVICE).
+        A CUDA tensor may still have work pending on torch's current stream for its device; unless the context was
+        created on that very stream, wait for it here — the context's own stream is non-blocking and takes no
+        implicit ordering from torch's streams."""
+        if getattr(data, "is_cuda", False):
+            import torch
+            s = torch.cuda.current_stream(data.device)
+            if not self._stream or s.cuda_stream != self._stream:
+                s.synchronize()
+
     # -- results
     def _take(self, resp, want_chunks: bool) -> ChunkList:
         r = resp.contents
@@ -224,6 +236,7 @@ class XetHasher:
     def hash_buffers(self, data, offsets: Sequence[int], memory: int = MEM_AUTO, want_chunks: bool = False) -> ChunkList:
         """Files packed back to back in `data` (bytes, numpy, torch tensor or raw address)."""
         addr, _, keep = _ptr_of(data)
+        self._order_after_torch(data)
         off = np.ascontiguousarray(offsets, dtype=np.uint64)
         n_files = max(off.size - 1, 0)
         resp = C.POINTER(L.XetGpuResult)()
@@ -270,12 +283,14 @@ class XetHasher:
 
     def verify_buffer(self, data, expected_hex: str, memory: int = MEM_AUTO) -> None:
         addr, n, keep = _ptr_of(data)
+        self._order_after_torch(data)
         _check(self._lib.xetgpu_verify_buffer(self._ctx, addr, n, memory, expected_hex.encode()))
         del keep
 
     # -- stage-level
     def gear_candidates(self, data, memory: int = MEM_AUTO) -> np.ndarray:
         addr, n, keep = _ptr_of(data)
+        self._order_after_torch(data)
         out = C.POINTER(C.c_uint64)()
         cnt = C.c_uint64()
         _check(self._lib.xetgpu_gear_candidates(self._ctx, addr, n, memory, C.byref(out), C.byref(cnt)))
@@ -287,6 +302,7 @@ class XetHasher:
     def hash_range(self, data, file_len: int, range_begin: int, range_end: int, entry_cut: int,
                    memory: int = MEM_AUTO) -> RangeResult:
         addr, _, keep = _ptr_of(data)
+        self._order_after_torch(data)
         resp = C.POINTER(L.XetGpuResult)()
         exit_cut = C.c_uint64()
         _check(self._lib.xetgpu_hash_range(self._ctx, addr, memory, file_len, range_begin, range_end, entry_cut,
@@ -298,6 +314,7 @@ class XetHasher:
     def range_exit_cut(self, data, file_len: int, range_begin: int, range_end: int, entry_cut: int,
                        memory: int = MEM_AUTO) -> int:
         addr, _, keep = _ptr_of(data)
+        self._order_after_torch(data)
         exit_cut = C.c_uint64()
         _check(self._lib.xetgpu_range_exit_cut(self._ctx, addr, memory, file_len, range_begin, range_end, entry_cut,
                                                C.byref(exit_cut)))
@@ -311,6 +328,7 @@ class XetHasher:
         fh = (C.c_uint8 * 32)()
         if hasattr(chunk_hashes, "data_ptr"):
             h, s = chunk_hashes.contiguous(), chunk_sizes.contiguous()
+            self._order_after_torch(h)
             assert h.element_size() == 1 and s.element_size() == 8 and h.numel() == 32 * s.numel()
             hp = C.cast(h.data_ptr(), C.POINTER(C.c_uint8))
             sp = C.cast(s.data_ptr(), C.POINTER(C.c_uint64))

@@ -174,22 +174,24 @@ def exchange_lead(piece: torch.Tensor, lead_capacity: int, ranges: Sequence[Tupl
     lead = min(begin, RANGE_LEAD) if n_own else 0
     if lead > lead_capacity:
         raise ValueError("headroom in front of the range is smaller than the halo")
+    # gloo moves host memory only: stage device tensors through the host when the group runs on it (single-GPU tests)
+    host_hop = piece.is_cuda and dist.get_backend(group) == "gloo"
     ops = []
     nxt = ranges[rank + 1] if rank + 1 < world else (0, 0)
     if nxt[1] > nxt[0]:                                    # the next rank needs my tail
         if n_own < RANGE_LEAD:
             raise ValueError("a range followed by a non-empty range must be at least RANGE_LEAD bytes")
         tail = piece[lead_capacity + n_own - RANGE_LEAD: lead_capacity + n_own].contiguous()
-        ops.append(dist.P2POp(dist.isend, tail, _peer(rank + 1, group), group))
+        ops.append(dist.P2POp(dist.isend, tail.cpu() if host_hop else tail, _peer(rank + 1, group), group))
     buf = None
     if lead:
-        buf = torch.empty(RANGE_LEAD, dtype=torch.uint8, device=piece.device)
+        buf = torch.empty(RANGE_LEAD, dtype=torch.uint8, device="cpu" if host_hop else piece.device)
         ops.append(dist.P2POp(dist.irecv, buf, _peer(rank - 1, group), group))
     if ops:
         for w in dist.batch_isend_irecv(ops):
             w.wait()
     if lead:
-        piece[lead_capacity - lead: lead_capacity] = buf[RANGE_LEAD - lead:]
+        piece[lead_capacity - lead: lead_capacity] = buf[RANGE_LEAD - lead:].to(piece.device)
     return lead
 
 
@@ -299,3 +301,102 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
         dist.send(pack(ends, hashes), _peer(0, group), group=group)
         _mark("gather_ms")
     return out
+
+
+# ------------------------------------------------------------- concatenated work (BASELINE config 4)
+PIECE_HEADROOM = 1 << 18   # bytes kept free in front of a partial piece: >= RANGE_LEAD, keeps the piece 256-byte aligned
+
+
+@dataclass
+class ConcatLayout:
+    """Where one rank keeps its pieces of a `plan_concatenated` plan inside one flat byte buffer."""
+    pieces: List[Piece]
+    offsets: List[int]        # buffer offset of the headroom (partial pieces) or of the first byte (whole files)
+    headroom: List[int]       # PIECE_HEADROOM for a piece that does not start at byte 0 of its file, else 0
+    nbytes: int               # buffer bytes needed
+
+    def data_offset(self, k: int) -> int:
+        return self.offsets[k] + self.headroom[k]
+
+
+def layout_pieces(pieces: Sequence[Piece]) -> ConcatLayout:
+    offs, heads, off = [], [], 0
+    for p in pieces:
+        head = PIECE_HEADROOM if p.begin > 0 else 0
+        offs.append(off)
+        heads.append(head)
+        off = (off + head + (p.end - p.begin) + 255) & ~255
+    return ConcatLayout(list(pieces), offs, heads, off + 256)
+
+
+def shared_files(plan: Sequence[Sequence[Piece]]):
+    """(owners: file -> ranks holding a piece of it, shared: files held by more than one rank, ascending)."""
+    owners = {}
+    for r, pieces in enumerate(plan):
+        for p in pieces:
+            owners.setdefault(p.file, []).append(r)
+    return owners, sorted(f for f, rs in owners.items() if len(rs) > 1)
+
+
+def hash_concatenated(engine, buf: torch.Tensor, lay: ConcatLayout, plan: Sequence[Sequence[Piece]], n_files: int,
+                      groups: dict, comm_device: Optional[torch.device] = None, phases: Optional[dict] = None,
+                      memory: int = 0):
+    """One pass over a `plan_concatenated` job.  Collective: every rank calls it with its own buffer/layout.
+
+    Files that lie inside one rank's range are hashed whole, all of them in one batched engine call; a file that
+    straddles a range boundary goes through the byte-range protocol (`exchange_lead` + `hash_file_by_ranges`)
+    inside its own process group `groups[file]` — even-numbered shared files first, then odd-numbered ones, so
+    that no rank waits on a chain of neighbours.  Returns (file_hashes uint8 [n_files, 32] on every rank,
+    max bytes any fix-up window re-hashed on this rank)."""
+    import time as _time
+    rank = dist.get_rank()
+    dev = comm_device or torch.device("cpu")
+    owners, shared = shared_files(plan)
+    out = torch.zeros(n_files, 32, dtype=torch.int32)
+    t0 = _time.perf_counter()
+    # 1. whole files of this rank: one batched call.  The alignment padding between files is described to the
+    #    engine as spacer "files" (their hashes are dropped).
+    whole = [(k, p) for k, p in enumerate(lay.pieces) if p.whole and p.file_len]
+    for p in lay.pieces:
+        if p.file_len == 0:   # an empty file has no bytes to lay out: ask the engine for its (all-zero) hash directly
+            fr = engine.hash_buffers(buf[:0], np.zeros(2, dtype=np.uint64), memory=memory).files[0]
+            out[p.file] = torch.frombuffer(bytearray(fr.file_hash), dtype=torch.uint8).to(torch.int32)
+    if whole:
+        marks = sorted({x for k, p in whole for x in (lay.offsets[k], lay.offsets[k] + p.file_len)})
+        offsets = np.asarray(marks, dtype=np.uint64)
+        cl = engine.hash_buffers(buf, offsets, memory=memory)
+        slot = {int(o): i for i, o in enumerate(marks[:-1])}
+        for k, p in whole:
+            fr = cl.files[slot[lay.offsets[k]]]
+            out[p.file] = torch.frombuffer(bytearray(fr.file_hash), dtype=torch.uint8).to(torch.int32)
+    if phases is not None:
+        phases["whole_files_ms"] = phases.get("whole_files_ms", 0.0) + (_time.perf_counter() - t0) * 1e3
+    # 2. shared files
+    rehashed = 0
+    for parity in (0, 1):
+        for j, f in enumerate(shared):
+            if j % 2 != parity or rank not in owners[f]:
+                continue
+            k = next(i for i, p in enumerate(lay.pieces) if p.file == f)
+            p, o, head = lay.pieces[k], lay.offsets[k], lay.headroom[k]
+            g = groups[f]
+            ranges = [(q.begin, q.end) for r in owners[f] for q in plan[r] if q.file == f]
+            view = buf[o: o + head + (p.end - p.begin)]
+            t1 = _time.perf_counter()
+            lead = exchange_lead(view, head, ranges, group=g)
+            if phases is not None:
+                phases["halo_exchange_ms"] = phases.get("halo_exchange_ms", 0.0) + (_time.perf_counter() - t1) * 1e3
+            res = hash_file_by_ranges(engine, view[head - lead:], lead, p.file_len, p.begin, p.end, group=g,
+                                      comm_device=dev, phases=phases)
+            rehashed = max(rehashed, res.rehashed_bytes)
+            if res.file_hash is not None:
+                out[f] = torch.frombuffer(bytearray(res.file_hash), dtype=torch.uint8).to(torch.int32)
+    # 3. every rank ends with every file hash (rows are non-zero on exactly one rank: a sum is a gather)
+    t2 = _time.perf_counter()
+    if dist.get_world_size() > 1:
+        t = out.to(dev)
+        dist.all_reduce(t)
+        out = t.cpu()
+    if phases is not None:
+        phases["result_allreduce_ms"] = phases.get("result_allreduce_ms", 0.0) + (_time.perf_counter() - t2) * 1e3
+    return out.to(torch.uint8).numpy(), rehashed

@@ -81,3 +81,55 @@ def test_two_rank_nccl_byte_ranges_and_file_partition():
     for i, n in enumerate([40 << 20, 3 << 20, 0, 25 << 20, 70001]):
         if n <= (3 << 20):
             assert hashes[i].tobytes() == xet_oracle.hash_file(xet_inputs.splitmix_bytes(900 + i, n)).file_hash
+
+
+def _ranges_on_one_gpu(rank, world, n, seed):
+    """hash_file_by_ranges with the CUDA engine, every rank on GPU 0, exchanges over gloo (host tensors)."""
+    import ome_b200
+    import xet_inputs
+    from ome_b200 import sharded
+    dev = torch.device("cuda", 0)
+    eng = ome_b200.XetHasher(device=0)
+    ranges = sharded.split_byte_ranges(n, world)
+    begin, end = ranges[rank]
+    cap = 1 << 18
+    host = torch.zeros(cap + (end - begin), dtype=torch.uint8)
+    host[cap:] = torch.from_numpy(xet_inputs.splitmix_bytes(seed, n)[begin:end].copy())
+    lead = sharded.exchange_lead(host, cap, ranges)                     # halo over gloo, on the host copy
+    piece = torch.zeros(host.numel() + 256, dtype=torch.uint8, device=dev)
+    piece[: host.numel()] = host.to(dev)
+    out = sharded.hash_file_by_ranges(eng, piece[cap - lead: cap + (end - begin)], lead, n, begin, end,
+                                      comm_device=torch.device("cpu"))
+    eng.close()
+    return dict(fh=out.file_hash, root=out.merkle_root, n=out.n_chunks_total, ends=out.chunk_ends.tolist(),
+                hashes=out.chunk_hashes.tobytes(), rehashed=out.rehashed_bytes, range=(begin, end))
+
+
+def test_three_range_protocol_on_one_gpu_matches_oracle():
+    """The full byte-range protocol (speculative pass, carried cut, fix-up window, splice at the first common cut,
+    rank-0 merkle combine) with three ranks sharing the one GPU of the test box, against the CPU oracle."""
+    import xet_inputs
+    import xet_oracle
+    from test_sharded_cpu import run_ranks
+    n, seed = (40 << 20) + 777, 86
+    out = run_ranks(3, _ranges_on_one_gpu, n, seed)
+    ref = xet_oracle.hash_file(xet_inputs.splitmix_bytes(seed, n))
+    assert out[0]["fh"] == ref.file_hash and out[0]["root"] == ref.merkle_root and out[0]["n"] == ref.chunk_ends.size
+    ends = [e for o in out for e in o["ends"]]
+    assert ends == [int(x) for x in ref.chunk_ends]
+    assert b"".join(o["hashes"] for o in out) == ref.chunk_hashes.tobytes()
+    for o in out[1:]:                                                  # fix-up re-hashed a window, not the range
+        assert 0 < o["rehashed"] <= (4 << 20) + 131136 < o["range"][1] - o["range"][0]
+
+
+def test_concatenated_plan_on_one_gpu_matches_oracle():
+    """BASELINE config-4 shape in miniature (files end to end, three byte ranges) with the CUDA engine."""
+    import xet_inputs
+    import xet_oracle
+    from test_sharded_cpu import _concatenated, run_ranks
+    sizes = [9 << 20, 0, 11 << 20, 70001, (7 << 20) + 5, 10 << 20]
+    out = run_ranks(3, _concatenated, sizes, "cuda")
+    hashes = np.frombuffer(out[0]["hashes"], dtype=np.uint8).reshape(-1, 32)
+    assert all(o["hashes"] == out[0]["hashes"] for o in out) and out[0]["shared"]
+    for f, n in enumerate(sizes):
+        assert hashes[f].tobytes() == xet_oracle.hash_file(xet_inputs.splitmix_bytes(300 + f, n)).file_hash, f

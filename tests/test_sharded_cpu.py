@@ -157,3 +157,43 @@ def test_plan_concatenated_tiles_every_file():
                 loads = [sum(p.end - p.begin for p in pieces) for pieces in plan]
                 assert max(loads) - min(loads) <= 2 * (sharded.RANGE_LEAD + 4096) + max(sizes) * 0 + 4096 * world \
                     or max(sizes) < sum(sizes) // world
+
+
+def _concatenated(rank, world, sizes, engine_kind="oracle"):
+    """BASELINE config-4 shape in miniature: files end to end, cut into `world` byte ranges."""
+    if engine_kind == "oracle":
+        from oracle_engine import OracleEngine
+        eng, dev = OracleEngine(), torch.device("cpu")
+    else:  # the CUDA engine, every rank on GPU 0 (single-GPU box); the exchanges stay on gloo / host tensors
+        import ome_b200
+        eng, dev = ome_b200.XetHasher(device=0), torch.device("cuda", 0)
+    plan = sharded.plan_concatenated(sizes, world)
+    owners, shared = sharded.shared_files(plan)
+    groups = {f: dist.new_group(ranks=owners[f]) for f in shared}
+    lay = sharded.layout_pieces(plan[rank])
+    buf = torch.zeros(lay.nbytes, dtype=torch.uint8)
+    for k, p in enumerate(lay.pieces):
+        if p.end > p.begin:
+            o = lay.data_offset(k)
+            buf[o:o + p.end - p.begin] = torch.from_numpy(xet_inputs.splitmix_bytes(300 + p.file, p.file_len)[p.begin:p.end].copy())
+    buf = buf.to(dev)
+    phases = {}
+    hashes, rehashed = sharded.hash_concatenated(eng, buf, lay, plan, len(sizes), groups, comm_device=torch.device("cpu"),
+                                                 phases=phases)
+    if engine_kind != "oracle":
+        eng.close()
+    return dict(hashes=hashes.tobytes(), rehashed=rehashed, shared=shared, phases=sorted(phases))
+
+
+@pytest.mark.parametrize("world,sizes", [
+    (2, [3 << 20, 0, 5 << 20, 70001, 2 << 20]),
+    (3, [6 << 20, 6 << 20, 6 << 20, 6 << 20]),
+    (3, [20 << 20]),                       # one file shared by all three ranks
+], ids=["w2-mixed", "w3-equal", "w3-onefile"])
+def test_concatenated_plan_gloo(world, sizes):
+    out = run_ranks(world, _concatenated, sizes)
+    assert all(o["hashes"] == out[0]["hashes"] for o in out)      # every rank ends with every file hash
+    hashes = np.frombuffer(out[0]["hashes"], dtype=np.uint8).reshape(-1, 32)
+    for f, n in enumerate(sizes):
+        assert hashes[f].tobytes() == xet_oracle.hash_file(xet_inputs.splitmix_bytes(300 + f, n)).file_hash, f
+    assert out[0]["shared"], "the shapes above are chosen so that at least one file straddles a range boundary"
