@@ -18,7 +18,10 @@
  *   - calls are synchronous (the reference blocks on its runtime) [pkg/xet/src/ffi.rs:190]
  *   - a context may be used from any thread; calls on one context are serialised
  *     internally; it must not be used during xetgpu_context_free  [pkg/xet/README.md:76,88]
- *   - progress / cancellation use the reference's callback shapes   [pkg/xet/xet.h:22-40]
+ *   - progress / cancellation use the reference's callback shapes   [pkg/xet/xet.h:22-40]; handlers run on
+ *     library threads with no library lock held, but the call that invokes them is still in progress: a handler
+ *     may call xetgpu_context_set_progress_callback / xetgpu_last_timings, while a hashing call on the same
+ *     context from inside a handler is refused with code 1 (it would wait for itself)
  *   - a no-op versioned symbol lets the cgo preamble fail at link time on a mismatch
  *                                                       [pkg/xet/xet.h:94; pkg/xet/xet.go:11-13]
  * No type in this header depends on CUDA or PyTorch; device pointers travel as void*.
@@ -176,7 +179,10 @@ XetError* xetgpu_hash_buffers(XetGpuContext* ctx, const void* data, const uint64
 
 /*
  * Hash files on disk: read through the pinned staging buffers and copied to the GPU
- * while earlier bytes are being hashed.  The verify-after-download entry point for
+ * while earlier bytes are being hashed.  Sizes come from stat() when the call is planned and are re-checked with
+ * fstat() on the descriptor each piece is read from: a file that is replaced, grows or shrinks while the call runs
+ * fails with XETGPU_ERR_IO instead of being hashed over stale extents.  Files are opened piece by piece, so a batch
+ * may name more files than the process may hold open.  The verify-after-download entry point for
  * model-agent [pkg/modelagent/gopher.go:1130-1149 has no verification today; the OCI
  * branch's MD5 pass at gopher.go:843-860 is the shape it mirrors].
  */
@@ -270,6 +276,29 @@ XetError* xetgpu_merkle_from_chunks_static(const uint8_t* device_chunk_hashes,
                                            const uint64_t* device_chunk_sizes, uint64_t n_chunks,
                                            uint8_t* device_out_merkle_root, uint8_t* device_out_file_hash,
                                            void* stream);
+
+/* ---- several GPUs from one process -----------------------------------------------------------------
+ * "context new(const int* devices, n, ...)".  model-agent is one process per node
+ * [cmd/model-agent/main.go:243-271]; a multi-device context lets that one process use every GPU of the node.
+ * It owns one XetGpuContext per listed device and runs one host thread per device per call.  The files of a call
+ * are laid end to end and cut into one equal byte range per device: a file inside a range is hashed whole by that
+ * device, a file that straddles a boundary is shared — each owner hashes its byte range (the XETGPU_RANGE_LEAD bytes
+ * in front of it come from the file), the 8-byte carried cut walks down the owners, an owner whose assumed entry
+ * was wrong re-hashes a 4 MiB window and splices at the first common cut, and the first owner's device combines the
+ * chunk lists (xetgpu_merkle_from_chunks).  Results are identical to the single-device calls.
+ * devices == NULL or n_devices == 0 selects every visible device.  config->device is ignored and config->stream
+ * must be NULL.  Small jobs use fewer devices (at least 64 MiB of work per device). */
+typedef struct XetGpuMulti XetGpuMulti;
+XetError* xetgpu_multi_new(const int32_t* devices, size_t n_devices, const XetGpuConfig* config, XetGpuMulti** out_ctx);
+void xetgpu_multi_free(XetGpuMulti* ctx);
+size_t xetgpu_multi_device_count(const XetGpuMulti* ctx);
+XetError* xetgpu_multi_set_progress_callback(XetGpuMulti* ctx, XetProgressCallback callback, void* user_data,
+                                             uint32_t throttle_ms);
+/* Same contracts as xetgpu_hash_files / xetgpu_verify_files. */
+XetError* xetgpu_multi_hash_files(XetGpuMulti* ctx, const char* const* paths, size_t n_files, uint32_t flags,
+                                  const XetCancellationToken* cancel_token, XetGpuResult** out_result);
+XetError* xetgpu_multi_verify_files(XetGpuMulti* ctx, const char* const* paths, const char* const* expected_hex,
+                                    size_t n_files, const XetCancellationToken* cancel_token, uint8_t* out_ok);
 
 /* K0: fill device memory with the SURVEY.md §8(d) counter-based splitmix64 stream:
  * dst[i] = byte (byte_off + i) of stream `seed`.  Benchmarks and tests only. */

@@ -4,7 +4,7 @@ Host-side mirror of the Go surface OME's pkg/xet would gain
 over the C ABI in include/xetgpu.h.  The compute lives in hand-written sm_100a CUDA kernels
 (ome_b200/csrc); this package never computes a hash on the CPU.
 """
-from .hasher import (ChunkList, FileHash, FileList, RangeResult, XetGpuError, XetHasher, hash_from_hex, hash_to_hex,  # noqa: F401
+from .hasher import (ChunkList, FileHash, FileList, RangeResult, XetGpuError, XetHasher, XetMultiHasher, hash_from_hex, hash_to_hex,  # noqa: F401
                      merkle_from_chunks_static)
 
-__all__ = ["XetHasher", "XetGpuError", "FileHash", "FileList", "ChunkList", "RangeResult", "hash_to_hex", "hash_from_hex"]
+__all__ = ["XetHasher", "XetMultiHasher", "XetGpuError", "FileHash", "FileList", "ChunkList", "RangeResult", "hash_to_hex", "hash_from_hex"]

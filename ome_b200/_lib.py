@@ -81,6 +81,14 @@ SIGNATURES = {
                                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]),
     "xetgpu_merkle_from_chunks_static": (ERRP, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                                 C.c_void_p]),
+    "xetgpu_multi_new": (ERRP, [C.POINTER(C.c_int32), C.c_size_t, C.POINTER(XetGpuConfig), C.POINTER(CTX)]),
+    "xetgpu_multi_free": (None, [CTX]),
+    "xetgpu_multi_device_count": (C.c_size_t, [CTX]),
+    "xetgpu_multi_set_progress_callback": (ERRP, [CTX, ProgressCallback, C.c_void_p, C.c_uint32]),
+    "xetgpu_multi_hash_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.c_size_t, C.c_uint32,
+                                       C.POINTER(XetCancellationToken), C.POINTER(C.POINTER(XetGpuResult))]),
+    "xetgpu_multi_verify_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.c_size_t,
+                                         C.POINTER(XetCancellationToken), C.POINTER(C.c_uint8)]),
     "xetgpu_fill_splitmix": (ERRP, [CTX, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
     "xetgpu_last_timings": (ERRP, [CTX, C.POINTER(XetGpuTimings)]),
     "xetgpu_free_error": (None, [ERRP]),

@@ -91,7 +91,9 @@ struct XetGpuContext {
     uint32_t sm_count = 148;
     uint64_t staging_bytes = 64ull << 20;
     uint64_t max_batch_bytes = 8ull << 30;
-    std::mutex mu;
+    std::mutex mu;                            // serialises the hashing entry points of this context
+    std::atomic<std::thread::id> owner{};     // thread inside a hashing call (re-entrancy from a callback is refused)
+    std::mutex cb_mu;                         // guards the progress fields and `last` (never held while a callback runs)
     // Two lanes: a lane is a stream with its own grow-only workspace, pinned metadata area and timing
     // events.  Lane 0 runs on the context's stream; batches of several files alternate between the lanes
     // so that one group's copies and gear pass overlap the previous group's hashing.
@@ -127,6 +129,32 @@ struct XetGpuContext {
     std::chrono::steady_clock::time_point last_progress;
 };
 
+// Entry-point lock.  Calls on one context serialise on c->mu.  A progress / cancellation callback runs on a thread
+// that is inside such a call; if it calls a hashing entry point of the SAME context it would wait for itself, so
+// that case is detected and refused with XETGPU_ERR_INVALID_CONFIG instead of deadlocking.
+struct CtxGuard {
+    XetGpuContext* c;
+    bool ok;
+    explicit CtxGuard(XetGpuContext* ctx) : c(ctx), ok(true) {
+        if (c->owner.load() == std::this_thread::get_id()) {
+            ok = false;
+            return;
+        }
+        c->mu.lock();
+        c->owner.store(std::this_thread::get_id());
+    }
+    ~CtxGuard() {
+        if (!ok) return;
+        c->owner.store(std::thread::id());
+        c->mu.unlock();
+    }
+};
+#define LOCK_CTX(c)                                                                                     \
+    CtxGuard _ctx_guard(c);                                                                             \
+    if (!_ctx_guard.ok)                                                                                 \
+    return make_error(XETGPU_ERR_INVALID_CONFIG, "re-entrant call: a progress or cancellation callback " \
+                                                 "called a hashing entry point of the context that is running it")
+
 constexpr size_t kReadSlots = 16;  // pinned 16 MiB slots of the file reader ring
 
 typedef XetGpuContext::Lane Lane;
@@ -152,6 +180,8 @@ static XetError* ensure_input(XetGpuContext* c, uint64_t bytes) {
     c->d_input_cap = bytes;
     return nullptr;
 }
+
+extern "C" void xetgpu_context_free(XetGpuContext* c);
 
 extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContext** out_ctx) {
     if (!out_ctx) return make_error(XETGPU_ERR_INVALID_CONFIG, "out_ctx is NULL");
@@ -179,34 +209,37 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
         if (config->max_batch_bytes) c->max_batch_bytes = config->max_batch_bytes;
         c->stream = (cudaStream_t)config->stream;
     }
+    // From here on every failure tears the context down through xetgpu_context_free, which is NULL-tolerant per member.
+    cudaError_t ce = cudaSuccess;
+    auto ok = [&](cudaError_t r) {
+        if (ce == cudaSuccess && r != cudaSuccess) ce = r;
+        return ce == cudaSuccess;
+    };
     if (!c->stream) {
-        cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-        if (se != cudaSuccess) {
-            delete c;
-            return cuda_error(se, "cudaStreamCreateWithFlags");
-        }
-        c->own_stream = true;
+        if (ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking))) c->own_stream = true;
     }
     c->lanes[0].stream = c->stream;
-    cudaStreamCreateWithFlags(&c->lanes[1].stream, cudaStreamNonBlocking);
+    ok(cudaStreamCreateWithFlags(&c->lanes[1].stream, cudaStreamNonBlocking));
     for (auto& l : c->lanes) {
-        for (auto& ev : l.ev) cudaEventCreate(&ev);
-        for (auto& ev : l.ev_kernel) cudaEventCreate(&ev);
+        for (auto& ev : l.ev) ok(cudaEventCreate(&ev));
+        for (auto& ev : l.ev_kernel) ok(cudaEventCreate(&ev));
     }
-    cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
-    for (auto& ev : c->ev_gear_done) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    ok(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (auto& ev : c->ev_gear_done) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto& ev : c->stage_free) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     if (const char* v = getenv("XETGPU_TWO_LANES")) c->force_lanes = atoi(v) ? 1 : 0;
     if (const char* v = getenv("XETGPU_MIN_GROUP_BYTES")) {  // test knob: exercise the two-lane path on small inputs
         unsigned long long n = strtoull(v, nullptr, 10);
         if (n) c->min_group_bytes = n;
     }
-    for (auto& ev : c->stage_free) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
-    init_gear_kernels();
-    init_chunk_hash_kernels();
-    cudaError_t le = cudaGetLastError();
-    if (le != cudaSuccess) {
-        delete c;
-        return cuda_error(le, "kernel attribute setup");
+    if (ce == cudaSuccess) {
+        init_gear_kernels();
+        init_chunk_hash_kernels();
+        ce = cudaGetLastError();
+    }
+    if (ce != cudaSuccess) {
+        xetgpu_context_free(c);
+        return cuda_error(ce, "context set-up (streams, events, kernel attributes)");
     }
     {
         unsigned hc = std::thread::hardware_concurrency();
@@ -223,7 +256,7 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
 extern "C" void xetgpu_context_free(XetGpuContext* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& l : c->lanes) {
         if (l.stream) cudaStreamSynchronize(l.stream);
         if (l.ws.base) cudaFree(l.ws.base);
@@ -245,28 +278,37 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
     for (auto& ev : c->read_slot_ev) cudaEventDestroy(ev);
     for (auto& ev : c->stage_free)
         if (ev) cudaEventDestroy(ev);
-    if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 
 extern "C" XetError* xetgpu_context_set_progress_callback(XetGpuContext* c, XetProgressCallback callback,
                                                           void* user_data, uint32_t throttle_ms) {
     if (!c) return make_error(XETGPU_ERR_INVALID_CONFIG, "ctx is NULL");
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> lk(c->cb_mu);
     c->progress = callback;
     c->progress_user = user_data;
     c->throttle_ms = throttle_ms;
     return nullptr;
 }
 
+// The handler is copied under cb_mu and invoked with no library lock held, so it may call
+// xetgpu_context_set_progress_callback / xetgpu_last_timings on the same context.
 static void report_progress(XetGpuContext* c, const XetProgressUpdate& u, bool force) {
-    if (!c->progress) return;
-    auto now = std::chrono::steady_clock::now();
-    if (!force && c->throttle_ms &&
-        std::chrono::duration_cast<std::chrono::milliseconds>(now - c->last_progress).count() < c->throttle_ms)
-        return;
-    c->last_progress = now;
-    c->progress(&u, c->progress_user);
+    XetProgressCallback cb;
+    void* user;
+    {
+        std::lock_guard<std::mutex> lk(c->cb_mu);
+        if (!c->progress) return;
+        auto now = std::chrono::steady_clock::now();
+        if (!force && c->throttle_ms &&
+            std::chrono::duration_cast<std::chrono::milliseconds>(now - c->last_progress).count() < c->throttle_ms)
+            return;
+        c->last_progress = now;
+        cb = c->progress;
+        user = c->progress_user;
+    }
+    cb(&u, user);
 }
 
 // --------------------------------------------------------------------------------- hex helpers
@@ -442,10 +484,12 @@ static XetError* ensure_workspace(Lane* l, const Plan& p, PipelineBuffers* b) {
 // copies land in disjoint device ranges, so their order on the stream does not matter) and the slot
 // is reused once that copy's event has fired.
 struct ReadPiece {
-    int fd;               // file to pread() from, or -1 ...
-    const uint8_t* mem;   // ... for a piece of (pageable) host memory to memcpy
+    int fd;               // >= 0: a piece of file paths[file], opened by the worker for this piece only (a batch may
+                          //       hold more files than the process may keep open); -1: a piece of host memory
+    const uint8_t* mem;   // the host memory to memcpy when fd < 0
     uint64_t file_off, len, dev_off;
-    size_t file;          // index into paths (for error text)
+    size_t file;          // index into paths
+    uint64_t file_size;   // size the batch was planned with; the file must still have it when the piece is read
 };
 
 struct ReaderPool {
@@ -461,6 +505,7 @@ struct ReaderPool {
     std::condition_variable cv;
     std::atomic<size_t> next{0};
     std::atomic<uint64_t> bytes_done{0};
+    std::atomic<size_t> last_file{0};   // file of the piece read most recently (progress: current_file)
     std::atomic<bool> stop{false};
     XetError* err = nullptr;
 
@@ -487,20 +532,44 @@ struct ReaderPool {
             cudaEventSynchronize(slot_ev[s]);  // ... and the last copy out of this slot (any stream, any call) has drained
             const ReadPiece& p = pieces[i];
             uint64_t got = 0;
+            int fd = -1;
             if (p.fd < 0) {
                 memcpy(slots[s], p.mem, p.len);
                 got = p.len;
+            } else {
+                // open, then fstat the descriptor: the size is checked on the very object that is read, so a file
+                // replaced or resized since the batch was planned is an I/O error, never a hash of stale extents
+                fd = open(paths[p.file], O_RDONLY | O_CLOEXEC);
+                struct stat st;
+                if (fd < 0 || fstat(fd, &st) != 0) {
+                    XetError* e = make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
+                                             std::string("cannot open file: ") + strerror(errno), paths[p.file]);
+                    if (fd >= 0) close(fd);
+                    fail(e);
+                    return;
+                }
+                if ((uint64_t)st.st_size != p.file_size) {
+                    close(fd);
+                    fail(make_error(XETGPU_ERR_IO, "file changed size while being hashed", paths[p.file]));
+                    return;
+                }
             }
             while (got < p.len) {
-                ssize_t r = pread(p.fd, slots[s] + got, p.len - got, (off_t)(p.file_off + got));
+                ssize_t r = pread(fd, slots[s] + got, p.len - got, (off_t)(p.file_off + got));
                 if (r < 0 && errno == EINTR) continue;
                 if (r <= 0) {
-                    fail(make_error(XETGPU_ERR_IO, r < 0 ? std::string("read failed: ") + strerror(errno)
-                                                          : std::string("file shrank while being read"),
-                                    paths ? paths[p.file] : ""));
+                    XetError* e = make_error(XETGPU_ERR_IO, r < 0 ? std::string("read failed: ") + strerror(errno)
+                                                                  : std::string("file shrank while being read"),
+                                             paths ? paths[p.file] : "");
+                    close(fd);
+                    fail(e);
                     return;
                 }
                 got += (uint64_t)r;
+            }
+            if (fd >= 0) {
+                close(fd);
+                last_file.store(p.file);
             }
             cudaError_t ce = cudaMemcpyAsync(d_base + p.dev_off, slots[s], p.len, cudaMemcpyHostToDevice, stream);
             if (ce == cudaSuccess) ce = cudaEventRecord(slot_ev[s], stream);
@@ -581,7 +650,7 @@ static XetError* ingest_host(XetGpuContext* c, cudaStream_t stream, const uint8_
         pool.stream = stream;
         pool.d_base = d_dst;
         for (uint64_t o = 0; o < bytes; o += c->read_slot_bytes)
-            pool.pieces.push_back(ReadPiece{-1, src + o, 0, std::min<uint64_t>(c->read_slot_bytes, bytes - o), o, 0});
+            pool.pieces.push_back(ReadPiece{-1, src + o, 0, std::min<uint64_t>(c->read_slot_bytes, bytes - o), o, 0, 0});
         return run_reader_pool(c, pool, [](ReaderPool&) {});
     }
     if (XetError* e = ensure_staging(c)) return e;
@@ -840,6 +909,7 @@ static XetError* build_result(const ResultBuilder& rb, bool want_chunks, XetGpuR
 }
 
 static void publish_timings(XetGpuContext* c, const ResultBuilder& rb, uint64_t bytes, float wall_ms) {
+    std::lock_guard<std::mutex> lk(c->cb_mu);
     XetGpuTimings& t = c->last;
     t.h2d_ms = rb.h2d_ms;
     t.gear_ms = rb.gear_ms;
@@ -1045,7 +1115,7 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
             return make_error(XETGPU_ERR_INVALID_CONFIG, "offsets must be ascending");
     if (n_files && offsets[n_files] > offsets[0] && !data)
         return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
     std::vector<uint64_t> rel(n_files + 1, 0);
     const uint64_t lo = n_files ? offsets[0] : 0;
@@ -1063,119 +1133,207 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
 }
 
 // -------------------------------------------------------------------------------------- files
+static XetError* stat_regular(const char* path, uint64_t* size) {
+    struct stat st;
+    if (stat(path, &st) != 0)
+        return make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
+                          std::string("cannot stat file: ") + strerror(errno), path);
+    if (!S_ISREG(st.st_mode)) return make_error(XETGPU_ERR_IO, "not a regular file", path);
+    *size = (uint64_t)st.st_size;
+    return nullptr;
+}
+
+static bool cancelled(const XetCancellationToken* cancel) {
+    return cancel && cancel->callback && cancel->callback(cancel->user_data);
+}
+
+// Progress of one xetgpu_hash_files call (or of one device's share of a multi-device call).
+struct FileProgress {
+    XetGpuContext* report_to = nullptr;   // context whose handler receives the updates
+    std::atomic<uint64_t>* shared_bytes = nullptr;  // multi-device: bytes completed by all devices together
+    std::atomic<uint32_t>* shared_files = nullptr;  // multi-device: files completed by all devices together
+    XetProgressUpdate pu{};
+};
+
+// Reads byte ranges of files into c->d_input through the reader pool.  Caller holds the context.
+struct FileSpan {
+    size_t file;            // index into paths
+    uint64_t off, len;      // range of the file
+    uint64_t file_size;
+};
+
+static XetError* read_spans_to_device(XetGpuContext* c, const char* const* paths, const std::vector<FileSpan>& spans,
+                                      std::vector<uint64_t>* rel, const XetCancellationToken* cancel,
+                                      FileProgress* prog, uint64_t bytes_before) {
+    uint64_t bytes = 0;
+    for (const auto& sp : spans) bytes += sp.len;
+    if (XetError* e = ensure_input(c, bytes)) return e;
+    if (XetError* e = ensure_read_slots(c)) return e;
+    ReaderPool pool;
+    pool.paths = paths;
+    pool.stream = c->stream;
+    pool.d_base = c->d_input;
+    rel->assign(spans.size() + 1, 0);
+    uint64_t dev_off = 0;
+    for (size_t k = 0; k < spans.size(); k++) {
+        const FileSpan& sp = spans[k];
+        (*rel)[k] = dev_off;
+        for (uint64_t o = 0; o < sp.len; o += c->read_slot_bytes)
+            pool.pieces.push_back(ReadPiece{0, nullptr, sp.off + o, std::min<uint64_t>(c->read_slot_bytes, sp.len - o),
+                                            dev_off + o, sp.file, sp.file_size});
+        dev_off += sp.len;
+    }
+    (*rel)[spans.size()] = dev_off;
+    // this thread reports progress and polls for cancellation while the readers work
+    uint64_t reported = 0;
+    return run_reader_pool(c, pool, [&](ReaderPool& pl) {
+        if (prog && prog->report_to) {
+            const uint64_t done = pl.bytes_done.load();
+            if (prog->shared_bytes) {
+                prog->pu.completed_bytes = prog->shared_bytes->fetch_add(done - reported) + (done - reported);
+                reported = done;
+            } else {
+                prog->pu.completed_bytes = bytes_before + done;
+            }
+            prog->pu.current_file = paths[pl.last_file.load()];
+            report_progress(prog->report_to, prog->pu, false);
+        }
+        if (cancelled(cancel)) pl.fail(make_error(XETGPU_ERR_CANCELLED, "cancelled"));
+    });
+}
+
+// Hash whole files (paths[idx[k]] for k in [0, n)) on context c, batch by batch.  Results land in files_out[idx[k]]
+// and, with want_chunks, in the per-file chunk vectors.  Caller holds the context.
+struct FileChunks {
+    std::vector<uint64_t> ends;
+    std::vector<uint8_t> hashes;
+};
+
+static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, const std::vector<size_t>& idx,
+                                  const std::vector<uint64_t>& sizes, bool want_chunks, const XetCancellationToken* cancel,
+                                  FileProgress* prog, XetGpuFileResult* files_out, std::vector<FileChunks>* chunks_out) {
+    uint64_t bytes_before = 0;
+    size_t k0 = 0;
+    while (k0 < idx.size()) {
+        // batch = as many whole files as fit in max_batch_bytes (at least one)
+        size_t k1 = k0;
+        uint64_t bytes = 0;
+        while (k1 < idx.size() && (k1 == k0 || bytes + sizes[idx[k1]] <= c->max_batch_bytes)) bytes += sizes[idx[k1++]];
+        if (cancelled(cancel)) return make_error(XETGPU_ERR_CANCELLED, "cancelled");
+        std::vector<FileSpan> spans;
+        for (size_t k = k0; k < k1; k++) spans.push_back(FileSpan{idx[k], 0, sizes[idx[k]], sizes[idx[k]]});
+        std::vector<uint64_t> rel;
+        if (XetError* e = read_spans_to_device(c, paths, spans, &rel, cancel, prog, bytes_before)) return e;
+        bytes_before += bytes;
+        if (prog && prog->report_to) {
+            if (!prog->shared_bytes) {
+                prog->pu.completed_bytes = bytes_before;
+                prog->pu.completed_files = (uint32_t)k1;
+            } else if (prog->shared_files) {
+                prog->pu.completed_files = prog->shared_files->fetch_add((uint32_t)(k1 - k0)) + (uint32_t)(k1 - k0);
+            }
+            report_progress(prog->report_to, prog->pu, false);
+        }
+        RunOptions opt;
+        opt.want_chunks = want_chunks;
+        XetGpuResult* part = nullptr;
+        if (XetError* e = run_pipeline(c, c->d_input, rel.data(), k1 - k0, opt, &part)) return e;
+        for (size_t k = k0; k < k1; k++) {
+            const XetGpuFileResult& fr = part->files[k - k0];
+            files_out[idx[k]] = fr;
+            if (want_chunks && chunks_out && fr.n_chunks) {
+                FileChunks& fc = (*chunks_out)[idx[k]];
+                fc.ends.assign(part->chunk_ends + fr.first_chunk, part->chunk_ends + fr.first_chunk + fr.n_chunks);
+                fc.hashes.assign(part->chunk_hashes + fr.first_chunk * 32, part->chunk_hashes + (fr.first_chunk + fr.n_chunks) * 32);
+            }
+        }
+        xetgpu_free_result(part);
+        k0 = k1;
+    }
+    return nullptr;
+}
+
+// Per-file results + per-file chunk vectors -> one XetGpuResult (files in caller order, chunks file by file).
+static XetError* assemble_result(std::vector<XetGpuFileResult>& files, std::vector<FileChunks>& chunks, bool want_chunks,
+                                 XetGpuResult** out_result) {
+    XetGpuResult* total = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
+    if (!total) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+    total->n_files = files.size();
+    total->files = (XetGpuFileResult*)calloc(files.size() ? files.size() : 1, sizeof(XetGpuFileResult));
+    if (!total->files) {
+        free(total);
+        return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+    }
+    uint64_t n_chunks = 0;
+    for (size_t f = 0; f < files.size(); f++) {
+        files[f].first_chunk = want_chunks ? n_chunks : 0;
+        if (want_chunks) n_chunks += chunks[f].ends.size();
+        total->files[f] = files[f];
+    }
+    if (want_chunks && n_chunks) {
+        total->n_chunks = n_chunks;
+        total->chunk_ends = (uint64_t*)malloc(n_chunks * 8);
+        total->chunk_hashes = (uint8_t*)malloc(n_chunks * 32);
+        if (!total->chunk_ends || !total->chunk_hashes) {
+            xetgpu_free_result(total);
+            return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+        }
+        uint64_t w = 0;
+        for (size_t f = 0; f < files.size(); f++) {
+            const FileChunks& fc = chunks[f];
+            if (fc.ends.empty()) continue;
+            memcpy(total->chunk_ends + w, fc.ends.data(), fc.ends.size() * 8);
+            memcpy(total->chunk_hashes + w * 32, fc.hashes.data(), fc.hashes.size());
+            w += fc.ends.size();
+        }
+    }
+    *out_result = total;
+    return nullptr;
+}
+
 extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* paths, size_t n_files, uint32_t flags,
                                        const XetCancellationToken* cancel, XetGpuResult** out_result) {
     if (!c || !out_result || (n_files && !paths))
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_hash_files");
     *out_result = nullptr;
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
-    if (XetError* e = ensure_read_slots(c)) return e;
     std::vector<uint64_t> sizes(n_files);
     uint64_t all_bytes = 0;
     for (size_t f = 0; f < n_files; f++) {
         if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
-        struct stat st;
-        if (stat(paths[f], &st) != 0)
-            return make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
-                              std::string("cannot stat file: ") + strerror(errno), paths[f]);
-        if (!S_ISREG(st.st_mode)) return make_error(XETGPU_ERR_IO, "not a regular file", paths[f]);
-        sizes[f] = (uint64_t)st.st_size;
+        if (XetError* e = stat_regular(paths[f], &sizes[f])) return e;
         all_bytes += sizes[f];
     }
     const bool want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
-    XetGpuResult* total = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
-    total->n_files = n_files;
-    total->files = (XetGpuFileResult*)calloc(n_files ? n_files : 1, sizeof(XetGpuFileResult));
-    std::vector<uint64_t> all_ends;
-    std::vector<uint8_t> all_hashes;
-    XetProgressUpdate pu{};
-    pu.phase = XET_PROGRESS_PHASE_SCANNING;
-    pu.total_bytes = all_bytes;
-    pu.total_files = (uint32_t)n_files;
-    uint64_t bytes_before = 0;
-    XetError* err = nullptr;
-    size_t f0 = 0;
-    while (f0 < n_files && !err) {
-        // batch = as many whole files as fit in max_batch_bytes (at least one)
-        size_t f1 = f0;
-        uint64_t bytes = 0;
-        while (f1 < n_files && (f1 == f0 || bytes + sizes[f1] <= c->max_batch_bytes)) bytes += sizes[f1++];
-        if ((err = ensure_input(c, bytes))) break;
-        if (cancel && cancel->callback && cancel->callback(cancel->user_data)) {
-            err = make_error(XETGPU_ERR_CANCELLED, "cancelled");
-            break;
-        }
-        std::vector<uint64_t> rel(f1 - f0 + 1, 0);
-        ReaderPool pool;
-        pool.paths = paths;
-        pool.stream = c->stream;
-        pool.d_base = c->d_input;
-        std::vector<int> fds;
-        uint64_t dev_off = 0;
-        for (size_t f = f0; f < f1; f++) {
-            rel[f - f0] = dev_off;
-            int fd = sizes[f] ? open(paths[f], O_RDONLY) : -1;
-            if (sizes[f] && fd < 0) {
-                err = make_error(errno == ENOENT ? XETGPU_ERR_NOT_FOUND : XETGPU_ERR_IO,
-                                 std::string("cannot open file: ") + strerror(errno), paths[f]);
-                break;
-            }
-            if (fd >= 0) fds.push_back(fd);
-            for (uint64_t o = 0; o < sizes[f]; o += c->read_slot_bytes)
-                pool.pieces.push_back(
-                    ReadPiece{fd, nullptr, o, std::min<uint64_t>(c->read_slot_bytes, sizes[f] - o), dev_off + o, f});
-            dev_off += sizes[f];
-        }
-        rel[f1 - f0] = dev_off;
-        if (!err)  // this thread reports progress and polls for cancellation while the readers work
-            err = run_reader_pool(c, pool, [&](ReaderPool& pl) {
-                pu.completed_bytes = bytes_before + pl.bytes_done.load();
-                report_progress(c, pu, false);
-                if (cancel && cancel->callback && cancel->callback(cancel->user_data))
-                    pl.fail(make_error(XETGPU_ERR_CANCELLED, "cancelled"));
-            });
-        for (int fd : fds) close(fd);
-        if (err) break;
-        bytes_before += bytes;
-        pu.completed_bytes = bytes_before;
-        pu.completed_files = (uint32_t)f1;
-        report_progress(c, pu, false);
-        RunOptions opt;
-        opt.want_chunks = want_chunks;
-        XetGpuResult* part = nullptr;
-        if ((err = run_pipeline(c, c->d_input, rel.data(), f1 - f0, opt, &part))) break;
-        for (size_t f = f0; f < f1; f++) {
-            total->files[f] = part->files[f - f0];
-            total->files[f].first_chunk += all_ends.size();
-        }
-        if (want_chunks && part->n_chunks) {
-            all_ends.insert(all_ends.end(), part->chunk_ends, part->chunk_ends + part->n_chunks);
-            all_hashes.insert(all_hashes.end(), part->chunk_hashes, part->chunk_hashes + part->n_chunks * 32);
-        }
-        xetgpu_free_result(part);
-        f0 = f1;
-    }
-    if (err) {
+    FileProgress prog;
+    prog.report_to = c;
+    prog.pu.phase = XET_PROGRESS_PHASE_SCANNING;
+    prog.pu.total_bytes = all_bytes;
+    prog.pu.total_files = (uint32_t)n_files;
+    std::vector<size_t> idx(n_files);
+    for (size_t f = 0; f < n_files; f++) idx[f] = f;
+    std::vector<XetGpuFileResult> files(n_files);
+    std::vector<FileChunks> chunks(want_chunks ? n_files : 0);
+    if (XetError* e = hash_whole_files(c, paths, idx, sizes, want_chunks, cancel, &prog, files.data(),
+                                       want_chunks ? &chunks : nullptr)) {
         cudaStreamSynchronize(c->stream);
-        xetgpu_free_result(total);
-        return err;
+        return e;
     }
-    if (want_chunks && !all_ends.empty()) {
-        total->n_chunks = all_ends.size();
-        total->chunk_ends = (uint64_t*)malloc(all_ends.size() * 8);
-        total->chunk_hashes = (uint8_t*)malloc(all_hashes.size());
-        memcpy(total->chunk_ends, all_ends.data(), all_ends.size() * 8);
-        memcpy(total->chunk_hashes, all_hashes.data(), all_hashes.size());
-    }
-    pu.phase = XET_PROGRESS_PHASE_FINALIZING;
-    pu.current_file = nullptr;
-    report_progress(c, pu, true);
-    *out_result = total;
+    if (XetError* e = assemble_result(files, chunks, want_chunks, out_result)) return e;
+    prog.pu.phase = XET_PROGRESS_PHASE_FINALIZING;
+    prog.pu.completed_bytes = all_bytes;
+    prog.pu.completed_files = (uint32_t)n_files;
+    prog.pu.current_file = nullptr;
+    report_progress(c, prog.pu, true);
     return nullptr;
 }
 
 // ------------------------------------------------------------------------------------- verify
+static XetError* verify_against(const XetGpuResult* r, const char* const* paths, const char* const* expected_hex,
+                                const std::vector<std::vector<uint8_t>>& want, size_t n_files, uint8_t* out_ok);
+static XetError* parse_expected(const char* const* paths, const char* const* expected_hex, size_t n_files,
+                                std::vector<std::vector<uint8_t>>* want);
 static XetError* compare_hash(const uint8_t got[32], const char* expected_hex, const char* what) {
     uint8_t want[32];
     if (XetError* e = xetgpu_hash_from_hex(expected_hex, want)) return e;
@@ -1202,32 +1360,13 @@ extern "C" XetError* xetgpu_verify_files(XetGpuContext* c, const char* const* pa
                                          size_t n_files, const XetCancellationToken* cancel, uint8_t* out_ok) {
     if (!c || (n_files && (!paths || !expected_hex)))
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_verify_files");
-    std::vector<std::vector<uint8_t>> want(n_files);
-    for (size_t f = 0; f < n_files; f++) {
-        if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
-        if (expected_hex[f] && expected_hex[f][0]) {
-            want[f].resize(32);
-            if (XetError* e = xetgpu_hash_from_hex(expected_hex[f], want[f].data())) return e;
-        }
-    }
+    std::vector<std::vector<uint8_t>> want;
+    if (XetError* e = parse_expected(paths, expected_hex, n_files, &want)) return e;
     XetGpuResult* r = nullptr;
     if (XetError* e = xetgpu_hash_files(c, paths, n_files, 0, cancel, &r)) return e;
-    std::string bad;
-    size_t n_bad = 0;
-    for (size_t f = 0; f < n_files; f++) {
-        const bool ok = want[f].empty() || memcmp(r->files[f].file_hash, want[f].data(), 32) == 0;
-        if (out_ok) out_ok[f] = ok ? 1 : 0;
-        if (!ok) {
-            char hex[65];
-            xetgpu_hash_to_hex(r->files[f].file_hash, hex);
-            if (n_bad < 16) bad += std::string(paths[f]) + ": expected " + expected_hex[f] + " computed " + hex + "\n";
-            n_bad++;
-        }
-    }
+    XetError* e = verify_against(r, paths, expected_hex, want, n_files, out_ok);
     xetgpu_free_result(r);
-    if (!n_bad) return nullptr;
-    return make_error(XETGPU_ERR_CHECKSUM_MISMATCH,
-                      "xet hash mismatch for " + std::to_string(n_bad) + " of " + std::to_string(n_files) + " files", bad);
+    return e;
 }
 
 extern "C" XetError* xetgpu_verify_buffer(XetGpuContext* c, const void* data, uint64_t len, int32_t memory,
@@ -1251,7 +1390,7 @@ extern "C" XetError* xetgpu_gear_candidates(XetGpuContext* c, const void* data, 
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_gear_candidates");
     *out_indices = nullptr;
     *out_count = 0;
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
     if (len == 0) return nullptr;
     const uint8_t* d = nullptr;
@@ -1296,7 +1435,7 @@ static XetError* range_common(XetGpuContext* c, const void* data, int32_t memory
     if (entry_cut < data_pos || range_begin - entry_cut > XETGPU_MAX_CHUNK)
         return make_error(XETGPU_ERR_INVALID_CONFIG, "entry_cut must lie within one maximum chunk before range_begin");
     if (out_result) *out_result = nullptr;
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
     const uint64_t len = range_end - data_pos;
     if (len && !data) return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
@@ -1336,7 +1475,7 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
                                                uint8_t out_merkle_root[32], uint8_t out_file_hash[32]) {
     if (!c || !out_merkle_root || !out_file_hash || (n_chunks && (!chunk_hashes || !chunk_sizes)))
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_merkle_from_chunks");
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
     // a one-file plan whose slot range holds exactly n_chunks nodes
     Plan plan;
@@ -1376,7 +1515,7 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
 extern "C" XetError* xetgpu_fill_splitmix(XetGpuContext* c, void* device_dst, uint64_t seed, uint64_t byte_off,
                                           uint64_t len) {
     if (!c || (len && !device_dst)) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_fill_splitmix");
-    std::lock_guard<std::mutex> lk(c->mu);
+    LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
     launch_fill_splitmix((uint8_t*)device_dst, seed, byte_off, len, c->stream);
     CU(cudaGetLastError());
@@ -1386,7 +1525,356 @@ extern "C" XetError* xetgpu_fill_splitmix(XetGpuContext* c, void* device_dst, ui
 
 extern "C" XetError* xetgpu_last_timings(XetGpuContext* c, XetGpuTimings* out) {
     if (!c || !out) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_last_timings");
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::mutex> lk(c->cb_mu);
     *out = c->last;
     return nullptr;
+}
+
+// ------------------------------------------------------------------------------- several GPUs, one process
+// model-agent is ONE process per node (cmd/model-agent/main.go:243-271), so the node's GPUs are reached from one
+// address space: a multi-device context owns one XetGpuContext per device and one host thread per device per call.
+// Work is laid out like BASELINE config 4: the files end to end, cut into one equal byte range per device.  A file
+// inside a range is hashed whole by that device; a file that straddles a range boundary is shared: every owner
+// hashes its range speculatively (entry cut assumed at the range begin) with the RANGE_LEAD bytes in front of it
+// read from the file itself, then the true 8-byte carry walks down the owners on the host and an owner whose
+// assumption was wrong re-hashes a small window and splices at the first common cut (same protocol as
+// ome_b200/sharded.py, which does it across processes).  The merkle combine runs on the first owner's device.
+struct XetGpuMulti {
+    std::vector<XetGpuContext*> ctx;
+    std::mutex mu;
+    uint64_t min_bytes_per_device = 64ull << 20;  // below this much work per device, fewer devices are used
+};
+
+struct MultiPiece {
+    size_t file;
+    uint64_t begin, end, file_len;
+    bool whole() const { return begin == 0 && end == file_len; }
+};
+
+// Port of sharded.plan_concatenated: per device, its pieces in file order.
+static std::vector<std::vector<MultiPiece>> plan_concatenated(const std::vector<uint64_t>& sizes, size_t world,
+                                                              uint64_t align = 4096) {
+    std::vector<uint64_t> starts(sizes.size() + 1, 0);
+    for (size_t f = 0; f < sizes.size(); f++) starts[f + 1] = starts[f] + sizes[f];
+    const uint64_t total = starts[sizes.size()];
+    const uint64_t min_piece = XETGPU_RANGE_LEAD + align;
+    std::vector<uint64_t> cuts{0};
+    for (size_t r = 1; r < world; r++) {
+        const uint64_t pos = (uint64_t)((unsigned __int128)total * r / world);
+        size_t f = (size_t)(std::upper_bound(starts.begin(), starts.end(), pos) - starts.begin());
+        f = f ? f - 1 : 0;
+        if (f >= sizes.size()) f = sizes.size() - 1;
+        uint64_t off = (pos - starts[f]) / align * align;
+        if (off < min_piece) off = 0;
+        else if (sizes[f] - off < min_piece) off = sizes[f];
+        cuts.push_back(std::max(starts[f] + off, cuts.back()));
+    }
+    cuts.push_back(total);
+    std::vector<std::vector<MultiPiece>> plan(world);
+    for (size_t r = 0; r < world; r++) {
+        const uint64_t lo = cuts[r], hi = cuts[r + 1];
+        for (size_t f = 0; f < sizes.size(); f++) {
+            const uint64_t fb = starts[f], fe = starts[f] + sizes[f];
+            if (sizes[f] == 0) {
+                if ((lo <= fb && fb < hi) || (r == world - 1 && fb == total)) plan[r].push_back(MultiPiece{f, 0, 0, 0});
+                continue;
+            }
+            const uint64_t b = std::max(lo, fb), e = std::min(hi, fe);
+            if (b < e) plan[r].push_back(MultiPiece{f, b - fb, e - fb, sizes[f]});
+        }
+    }
+    return plan;
+}
+
+extern "C" XetError* xetgpu_multi_new(const int32_t* devices, size_t n_devices, const XetGpuConfig* config,
+                                      XetGpuMulti** out) {
+    if (!out) return make_error(XETGPU_ERR_INVALID_CONFIG, "out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return make_error(XETGPU_ERR_UNKNOWN, "no CUDA device available (libxetgpu has no CPU path)",
+                          e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    std::vector<int32_t> devs;
+    if (devices && n_devices) devs.assign(devices, devices + n_devices);
+    else
+        for (int d = 0; d < ndev; d++) devs.push_back(d);  // NULL / 0 = every visible device
+    // (a device may be listed more than once: it then runs that many workers — the single-GPU tests use this to
+    //  exercise the shared-file protocol)
+    if (config && config->stream)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "a multi-device context owns its streams: config->stream must be NULL");
+    XetGpuMulti* m = new XetGpuMulti();
+    if (const char* v = getenv("XETGPU_MULTI_MIN_BYTES")) {  // test knob: spread small jobs over the devices too
+        unsigned long long n = strtoull(v, nullptr, 10);
+        if (n) m->min_bytes_per_device = n;
+    }
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (int32_t d : devs) {
+        XetGpuConfig cfg{};
+        if (config) cfg = *config;
+        cfg.device = d;
+        cfg.stream = nullptr;
+        XetGpuContext* c = nullptr;
+        if (XetError* err = xetgpu_context_new(&cfg, &c)) {
+            for (auto* x : m->ctx) xetgpu_context_free(x);
+            delete m;
+            cudaSetDevice(prev);
+            return err;
+        }
+        m->ctx.push_back(c);
+    }
+    cudaSetDevice(prev);
+    *out = m;
+    return nullptr;
+}
+
+extern "C" void xetgpu_multi_free(XetGpuMulti* m) {
+    if (!m) return;
+    for (auto* c : m->ctx) xetgpu_context_free(c);
+    delete m;
+}
+
+extern "C" size_t xetgpu_multi_device_count(const XetGpuMulti* m) { return m ? m->ctx.size() : 0; }
+
+extern "C" XetError* xetgpu_multi_set_progress_callback(XetGpuMulti* m, XetProgressCallback callback, void* user_data,
+                                                        uint32_t throttle_ms) {
+    if (!m) return make_error(XETGPU_ERR_INVALID_CONFIG, "ctx is NULL");
+    return xetgpu_context_set_progress_callback(m->ctx[0], callback, user_data, throttle_ms);  // one handler, one throttle
+}
+
+// One owner's chunk list for its range of a shared file.
+struct RangePart {
+    std::vector<uint64_t> ends;     // file-relative
+    std::vector<uint8_t> hashes;
+    uint64_t exit_cut = 0;
+};
+
+// Caller holds c.  Reads [begin - lead, end) of the file and hashes the range from entry_cut.
+static XetError* hash_file_range_locked(XetGpuContext* c, const char* const* paths, const MultiPiece& p, uint64_t end,
+                                        uint64_t entry_cut, const XetCancellationToken* cancel, FileProgress* prog,
+                                        RangePart* out) {
+    const uint64_t lead = std::min<uint64_t>(p.begin, XETGPU_RANGE_LEAD);
+    const uint64_t data_pos = p.begin - lead;
+    std::vector<FileSpan> spans{FileSpan{p.file, data_pos, end - data_pos, p.file_len}};
+    std::vector<uint64_t> rel;
+    if (XetError* e = read_spans_to_device(c, paths, spans, &rel, cancel, prog, 0)) return e;
+    uint64_t offsets[2] = {0, end - data_pos};
+    RangeWalk rw{entry_cut - data_pos, end == p.file_len ? 1u : 0u};
+    RunOptions opt;
+    opt.range = &rw;
+    opt.end_bias = data_pos;
+    opt.want_chunks = true;
+    opt.skip_merkle = true;
+    uint64_t exit_abs = 0;
+    opt.exit_cut_abs = &exit_abs;
+    XetGpuResult* r = nullptr;
+    if (XetError* e = run_pipeline(c, c->d_input, offsets, 1, opt, &r)) return e;
+    out->exit_cut = exit_abs + data_pos;
+    out->ends.assign(r->chunk_ends, r->chunk_ends + r->n_chunks);
+    out->hashes.assign(r->chunk_hashes, r->chunk_hashes + r->n_chunks * 32);
+    xetgpu_free_result(r);
+    return nullptr;
+}
+
+// First cut of the re-synchronised chain `fix` that is also a cut of the speculative chain `spec`: the chunk that
+// ends there comes from `fix` (it starts elsewhere in the two chains), everything after it from `spec`.
+static bool splice_at_common_cut(const RangePart& fix, RangePart* spec) {
+    size_t i = 0, j = 0;
+    while (i < fix.ends.size() && j < spec->ends.size()) {
+        if (fix.ends[i] == spec->ends[j]) break;
+        if (fix.ends[i] < spec->ends[j]) i++;
+        else j++;
+    }
+    if (i >= fix.ends.size() || j >= spec->ends.size()) return false;
+    RangePart merged;
+    merged.ends.assign(fix.ends.begin(), fix.ends.begin() + i + 1);
+    merged.ends.insert(merged.ends.end(), spec->ends.begin() + j + 1, spec->ends.end());
+    merged.hashes.assign(fix.hashes.begin(), fix.hashes.begin() + (i + 1) * 32);
+    merged.hashes.insert(merged.hashes.end(), spec->hashes.begin() + (j + 1) * 32, spec->hashes.end());
+    merged.exit_cut = spec->exit_cut;
+    *spec = std::move(merged);
+    return true;
+}
+
+extern "C" XetError* xetgpu_multi_hash_files(XetGpuMulti* m, const char* const* paths, size_t n_files, uint32_t flags,
+                                             const XetCancellationToken* cancel, XetGpuResult** out_result) {
+    if (!m || !out_result || (n_files && !paths))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_multi_hash_files");
+    *out_result = nullptr;
+    std::lock_guard<std::mutex> lk(m->mu);
+    std::vector<uint64_t> sizes(n_files);
+    uint64_t all_bytes = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
+        if (XetError* e = stat_regular(paths[f], &sizes[f])) return e;
+        all_bytes += sizes[f];
+    }
+    const bool want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
+    const size_t world = (size_t)std::min<uint64_t>(m->ctx.size(), std::max<uint64_t>(1, all_bytes / m->min_bytes_per_device));
+    const auto plan = plan_concatenated(sizes, world);
+    std::vector<std::vector<size_t>> owners(n_files);   // devices that hold a piece of each file, ascending
+    for (size_t d = 0; d < world; d++)
+        for (const auto& p : plan[d]) owners[p.file].push_back(d);
+
+    std::vector<XetGpuFileResult> files(n_files);
+    std::vector<FileChunks> chunks(n_files);   // shared files need their lists whatever the flags say
+    std::vector<std::vector<RangePart>> parts(n_files);
+    for (size_t f = 0; f < n_files; f++) {
+        files[f].size = sizes[f];
+        if (owners[f].size() > 1) parts[f].resize(owners[f].size());
+    }
+    std::atomic<uint64_t> bytes_done{0};
+    std::atomic<uint32_t> files_done{0};
+    std::atomic<bool> stop{false};
+    // any device's failure cancels the others through the same token shape
+    struct Cancel {
+        const XetCancellationToken* user;
+        std::atomic<bool>* stop;
+    } cstate{cancel, &stop};
+    XetCancellationToken tok{[](void* u) -> bool {
+                                 Cancel* s = (Cancel*)u;
+                                 return s->stop->load() || cancelled(s->user);
+                             },
+                             &cstate};
+    std::vector<XetError*> errs(world, nullptr);
+    auto device_work = [&](size_t d) {
+        XetGpuContext* c = m->ctx[d];
+        CtxGuard g(c);
+        if (!g.ok) {
+            errs[d] = make_error(XETGPU_ERR_INVALID_CONFIG, "re-entrant call from a callback");
+            return;
+        }
+        if (cudaSetDevice(c->device) != cudaSuccess) {
+            errs[d] = make_error(XETGPU_ERR_UNKNOWN, "cudaSetDevice failed");
+            return;
+        }
+        FileProgress prog;
+        prog.report_to = m->ctx[0];
+        prog.shared_bytes = &bytes_done;
+        prog.shared_files = &files_done;
+        prog.pu.phase = XET_PROGRESS_PHASE_SCANNING;
+        prog.pu.total_bytes = all_bytes;
+        prog.pu.total_files = (uint32_t)n_files;
+        std::vector<size_t> whole;
+        for (const auto& p : plan[d])
+            if (p.whole()) whole.push_back(p.file);
+        errs[d] = hash_whole_files(c, paths, whole, sizes, want_chunks, &tok, &prog, files.data(), want_chunks ? &chunks : nullptr);
+        for (const auto& p : plan[d]) {
+            if (errs[d]) break;
+            if (p.whole()) continue;
+            size_t k = 0;
+            while (owners[p.file][k] != d) k++;
+            errs[d] = hash_file_range_locked(c, paths, p, p.end, p.begin /* assumed entry; exact for begin == 0 */, &tok,
+                                             &prog, &parts[p.file][k]);
+        }
+        if (errs[d]) stop.store(true);
+        cudaStreamSynchronize(c->stream);
+    };
+    std::vector<std::thread> threads;
+    for (size_t d = 1; d < world; d++) threads.emplace_back(device_work, d);
+    device_work(0);
+    for (auto& t : threads) t.join();
+    XetError* first = nullptr;
+    for (auto*& e : errs) {
+        // report the root cause, not the cancellations it triggered on the other devices
+        if (e && (!first || (first->code == XETGPU_ERR_CANCELLED && e->code != XETGPU_ERR_CANCELLED))) std::swap(first, e);
+        if (e) xetgpu_free_error(e);
+    }
+    if (first) return first;
+
+    // carry chain + merkle combine of the shared files (host side, a few small launches per boundary)
+    for (size_t f = 0; f < n_files; f++) {
+        if (owners[f].size() < 2) continue;
+        uint64_t entry = 0;
+        FileChunks& fc = chunks[f];
+        fc.ends.clear();
+        fc.hashes.clear();
+        for (size_t k = 0; k < owners[f].size(); k++) {
+            const size_t d = owners[f][k];
+            const MultiPiece* p = nullptr;
+            for (const auto& q : plan[d])
+                if (q.file == f) p = &q;
+            RangePart& spec = parts[f][k];
+            if (k > 0 && entry != p->begin) {
+                XetGpuContext* c = m->ctx[d];
+                CtxGuard g(c);
+                if (!g.ok) return make_error(XETGPU_ERR_INVALID_CONFIG, "re-entrant call from a callback");
+                CU(cudaSetDevice(c->device));
+                uint64_t window = 4ull << 20;
+                while (true) {
+                    const uint64_t w_end = std::min<uint64_t>(p->end, p->begin + window);
+                    RangePart fix;
+                    if (XetError* e = hash_file_range_locked(c, paths, *p, w_end, entry, cancel, nullptr, &fix)) return e;
+                    if (splice_at_common_cut(fix, &spec)) break;
+                    if (w_end == p->end) {   // the chains never met inside this range: the re-hash is the answer
+                        spec = std::move(fix);
+                        break;
+                    }
+                    window *= 4;
+                }
+            }
+            fc.ends.insert(fc.ends.end(), spec.ends.begin(), spec.ends.end());
+            fc.hashes.insert(fc.hashes.end(), spec.hashes.begin(), spec.hashes.end());
+            entry = spec.exit_cut;
+        }
+        std::vector<uint64_t> csz(fc.ends.size());
+        for (size_t i = 0; i < csz.size(); i++) csz[i] = fc.ends[i] - (i ? fc.ends[i - 1] : 0);
+        if (XetError* e = xetgpu_merkle_from_chunks(m->ctx[owners[f][0]], fc.hashes.data(), csz.data(), csz.size(),
+                                                    files[f].merkle_root, files[f].file_hash))
+            return e;
+        files[f].n_chunks = csz.size();
+    }
+    if (XetError* e = assemble_result(files, chunks, want_chunks, out_result)) return e;
+    XetProgressUpdate pu{};
+    pu.phase = XET_PROGRESS_PHASE_FINALIZING;
+    pu.total_bytes = pu.completed_bytes = all_bytes;
+    pu.total_files = pu.completed_files = (uint32_t)n_files;
+    report_progress(m->ctx[0], pu, true);
+    return nullptr;
+}
+
+static XetError* verify_against(const XetGpuResult* r, const char* const* paths, const char* const* expected_hex,
+                                const std::vector<std::vector<uint8_t>>& want, size_t n_files, uint8_t* out_ok) {
+    std::string bad;
+    size_t n_bad = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        const bool ok = want[f].empty() || memcmp(r->files[f].file_hash, want[f].data(), 32) == 0;
+        if (out_ok) out_ok[f] = ok ? 1 : 0;
+        if (!ok) {
+            char hex[65];
+            xetgpu_hash_to_hex(r->files[f].file_hash, hex);
+            if (n_bad < 16) bad += std::string(paths[f]) + ": expected " + expected_hex[f] + " computed " + hex + "\n";
+            n_bad++;
+        }
+    }
+    if (!n_bad) return nullptr;
+    return make_error(XETGPU_ERR_CHECKSUM_MISMATCH,
+                      "xet hash mismatch for " + std::to_string(n_bad) + " of " + std::to_string(n_files) + " files", bad);
+}
+
+static XetError* parse_expected(const char* const* paths, const char* const* expected_hex, size_t n_files,
+                                std::vector<std::vector<uint8_t>>* want) {
+    want->assign(n_files, {});
+    for (size_t f = 0; f < n_files; f++) {
+        if (!paths[f]) return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL path");
+        if (expected_hex[f] && expected_hex[f][0]) {
+            (*want)[f].resize(32);
+            if (XetError* e = xetgpu_hash_from_hex(expected_hex[f], (*want)[f].data())) return e;
+        }
+    }
+    return nullptr;
+}
+
+extern "C" XetError* xetgpu_multi_verify_files(XetGpuMulti* m, const char* const* paths, const char* const* expected_hex,
+                                               size_t n_files, const XetCancellationToken* cancel, uint8_t* out_ok) {
+    if (!m || (n_files && (!paths || !expected_hex)))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_multi_verify_files");
+    std::vector<std::vector<uint8_t>> want;
+    if (XetError* e = parse_expected(paths, expected_hex, n_files, &want)) return e;
+    XetGpuResult* r = nullptr;
+    if (XetError* e = xetgpu_multi_hash_files(m, paths, n_files, 0, cancel, &r)) return e;
+    XetError* e = verify_against(r, paths, expected_hex, want, n_files, out_ok);
+    xetgpu_free_result(r);
+    return e;
 }

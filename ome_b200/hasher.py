@@ -347,3 +347,77 @@ class XetHasher:
         t = L.XetGpuTimings()
         _check(self._lib.xetgpu_last_timings(self._ctx, C.byref(t)))
         return {k: getattr(t, k) for k, _ in L.XetGpuTimings._fields_}
+
+
+class XetMultiHasher:
+    """Every listed GPU of the node from ONE process (xetgpu_multi_* in include/xetgpu.h): what a single model-agent
+    process would hold.  Files are laid end to end and cut into one byte range per device; see the header."""
+
+    def __init__(self, devices: Optional[Sequence[int]] = None, staging_bytes: int = 0, max_batch_bytes: int = 0):
+        self._lib = L.load()
+        cfg = L.XetGpuConfig(-1, None, staging_bytes, max_batch_bytes, 0)
+        ctx = L.CTX()
+        if devices:
+            arr = (C.c_int32 * len(devices))(*devices)
+            _check(self._lib.xetgpu_multi_new(arr, len(devices), C.byref(cfg), C.byref(ctx)))
+        else:
+            _check(self._lib.xetgpu_multi_new(None, 0, C.byref(cfg), C.byref(ctx)))
+        self._ctx = ctx
+        self._cb = None
+
+    @property
+    def n_devices(self) -> int:
+        return int(self._lib.xetgpu_multi_device_count(self._ctx))
+
+    def close(self) -> None:
+        if getattr(self, "_ctx", None):
+            self._lib.xetgpu_multi_free(self._ctx)
+            self._ctx = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_progress_handler(self, handler: Optional[Callable[[dict], None]], throttle_ms: int = 200) -> None:
+        if handler is None:
+            self._cb = None
+            _check(self._lib.xetgpu_multi_set_progress_callback(self._ctx, L.ProgressCallback(0), None, 0))
+            return
+
+        def bridge(update, _user):
+            u = update.contents
+            handler(dict(phase=u.phase, total_bytes=u.total_bytes, completed_bytes=u.completed_bytes,
+                         total_files=u.total_files, completed_files=u.completed_files,
+                         current_file=(u.current_file or b"").decode(errors="replace")))
+
+        self._cb = L.ProgressCallback(bridge)
+        _check(self._lib.xetgpu_multi_set_progress_callback(self._ctx, self._cb, None, throttle_ms))
+
+    def hash_files(self, paths: Sequence[str], want_chunks: bool = False,
+                   should_cancel: Optional[Callable[[], bool]] = None) -> ChunkList:
+        arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+        tok = None
+        if should_cancel is not None:
+            cb = L.CancellationCallback(lambda _u: bool(should_cancel()))
+            tok = L.XetCancellationToken(cb, None)
+        resp = C.POINTER(L.XetGpuResult)()
+        _check(self._lib.xetgpu_multi_hash_files(self._ctx, arr, len(paths), WANT_CHUNKS if want_chunks else 0,
+                                                 C.byref(tok) if tok is not None else None, C.byref(resp)))
+        return XetHasher._take(self, resp, want_chunks)
+
+    def verify_files(self, paths: Sequence[str], expected_hex: Sequence[Optional[str]]) -> list:
+        n = len(paths)
+        assert len(expected_hex) == n
+        cp = (C.c_char_p * n)(*[p.encode() for p in paths])
+        ch = (C.c_char_p * n)(*[(h.encode() if h else None) for h in expected_hex])
+        ok = (C.c_uint8 * max(n, 1))()
+        _check(self._lib.xetgpu_multi_verify_files(self._ctx, cp, ch, n, None, ok))
+        return [bool(ok[i]) for i in range(n)]

@@ -1,0 +1,139 @@
+"""xetgpu_multi_* (several GPUs from one process) and the robustness rules of the file entry points, through the C ABI.
+
+On a single-GPU box the multi-device context is given the same device several times (one worker each), which
+exercises exactly the code that runs across real devices: the end-to-end layout, shared files with the carried cut,
+fix-up window, splice and merkle combine.  With two or more GPUs the same test also runs over all of them."""
+import os
+import resource
+
+import numpy as np
+import pytest
+
+import xet_inputs
+import xet_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _write(tmp_path, specs):
+    paths, datas = [], []
+    for i, spec in enumerate(specs):
+        d = xet_inputs.build(spec)
+        p = tmp_path / f"f{i}.bin"
+        d.tofile(p)
+        paths.append(str(p))
+        datas.append(d)
+    return paths, datas
+
+
+def _check(cl, datas):
+    for f, d in enumerate(datas):
+        ref = xet_oracle.hash_file(d)
+        fr = cl.files[f]
+        assert fr.size == d.size and fr.n_chunks == ref.chunk_ends.size, f
+        assert fr.file_hash == ref.file_hash, f
+        if ref.chunk_ends.size:
+            assert fr.merkle_root == ref.merkle_root, f
+        if cl.chunk_ends is not None:
+            ends, hashes = cl.chunks_of(f)
+            assert np.array_equal(ends, ref.chunk_ends) and np.array_equal(hashes, ref.chunk_hashes), f
+
+
+SPECS = [[["splitmix", 41, (9 << 20) + 1]], [], [["splitmix", 42, 11 << 20]], [["splitmix", 43, 70001]],
+         [["splitmix", 44, 1 << 20], ["zeros", 6 << 20]],          # shared-file chains that cannot re-merge
+         [["splitmix", 45, (10 << 20) + 77]]]
+
+
+@pytest.mark.parametrize("devices", [[0], [0, 0], [0, 0, 0], None], ids=["one", "two-workers", "three-workers", "all-gpus"])
+def test_multi_hash_files_matches_oracle(tmp_path, monkeypatch, devices):
+    import ome_b200
+    monkeypatch.setenv("XETGPU_MULTI_MIN_BYTES", str(1 << 20))
+    paths, datas = _write(tmp_path, SPECS)
+    with ome_b200.XetMultiHasher(devices) as m:
+        seen = []
+        m.set_progress_handler(seen.append, throttle_ms=0)
+        cl = m.hash_files(paths, want_chunks=True)
+        _check(cl, datas)
+        assert seen and seen[-1]["completed_bytes"] == sum(d.size for d in datas) and seen[-1]["phase"] == 2
+        _check(m.hash_files(paths), datas)
+        good = [f.hex for f in cl.files]
+        assert m.verify_files(paths, good) == [True] * len(paths)
+        with pytest.raises(ome_b200.XetGpuError) as ei:
+            m.verify_files(paths, good[:2] + ["0" * 64] + good[3:])
+        assert ei.value.code == 6 and paths[2] in ei.value.details
+        with pytest.raises(ome_b200.XetGpuError) as ei:
+            m.hash_files(paths, should_cancel=lambda: True)
+        assert ei.value.code == 7
+        with pytest.raises(ome_b200.XetGpuError) as ei:
+            m.hash_files(paths + [str(tmp_path / "missing")])
+        assert ei.value.code == 4
+
+
+def test_multi_one_large_file_split_over_workers(tmp_path, monkeypatch):
+    """One file shared by every worker (the single-huge-checkpoint case)."""
+    import ome_b200
+    monkeypatch.setenv("XETGPU_MULTI_MIN_BYTES", str(1 << 20))
+    paths, datas = _write(tmp_path, [[["splitmix", 46, (48 << 20) + 12345]]])
+    with ome_b200.XetMultiHasher([0, 0, 0, 0]) as m:
+        _check(m.hash_files(paths, want_chunks=True), datas)
+
+
+def test_more_files_than_open_file_limit(hasher, tmp_path):
+    """Files are opened piece by piece: a batch may name more files than RLIMIT_NOFILE allows to be open at once."""
+    specs = [[["splitmix", 500 + i, 3000 + 37 * i]] for i in range(160)]
+    paths, datas = _write(tmp_path, specs)
+    soft, hard = resource.getrlimit(resource.RLIMIT_NOFILE)
+    in_use = len(os.listdir("/proc/self/fd"))
+    resource.setrlimit(resource.RLIMIT_NOFILE, (in_use + 40, hard))
+    try:
+        cl = hasher.hash_files(paths)
+    finally:
+        resource.setrlimit(resource.RLIMIT_NOFILE, (soft, hard))
+    _check(cl, datas)
+
+
+def test_file_resized_during_hash_is_an_io_error(hasher, tmp_path):
+    import ome_b200
+    p = tmp_path / "big.bin"
+    n = 1 << 30
+    with open(p, "wb") as f:
+        f.truncate(n)                      # sparse: reads as zeros
+    state = {"done": False}
+
+    def shrink(_u):
+        if not state["done"]:
+            state["done"] = True
+            os.truncate(p, n // 2)
+
+    hasher.set_progress_handler(shrink, throttle_ms=0)
+    try:
+        with pytest.raises(ome_b200.XetGpuError) as ei:
+            hasher.hash_files([str(p)])
+    finally:
+        hasher.set_progress_handler(None)
+    assert ei.value.code == 8 and state["done"]          # IoError: size changed / file shrank
+
+
+def test_reentrant_call_from_progress_handler_is_refused(hasher, tmp_path):
+    import ome_b200
+    paths, datas = _write(tmp_path, [[["splitmix", 47, 40 << 20]]])
+    got = {}
+
+    def handler(_u):
+        if "err" in got:
+            return
+        try:
+            hasher.hash_bytes(b"abc")                     # hashing entry point of the context that is running us
+            got["err"] = None
+        except ome_b200.XetGpuError as e:
+            got["err"] = e
+        got["timings"] = hasher.last_timings()            # ... while the bookkeeping calls are allowed
+
+    hasher.set_progress_handler(handler, throttle_ms=0)
+    try:
+        cl = hasher.hash_files(paths)
+    finally:
+        hasher.set_progress_handler(None)
+    _check(cl, datas)
+    assert got["err"] is not None and got["err"].code == 1 and "re-entrant" in got["err"].message
+    assert "total_ms" in got["timings"]
