@@ -265,7 +265,8 @@ XetError* xetgpu_merkle_from_chunks(XetGpuContext* ctx, const uint8_t* chunk_has
  * is a fixed array inside the library image (about 2.2 MB per GPU that loads the library, held
  * until exit), which caps the list at XETGPU_STATIC_MERKLE_MAX_CHUNKS entries; longer lists get
  * error code 1.  Inputs and outputs are DEVICE pointers owned by the caller (hashes: 32 bytes
- * per chunk, raw digest order; sizes: u64; outputs: 32 bytes each).  One kernel is launched on
+ * per chunk, raw digest order; sizes: u64; outputs: 32 bytes each; hash and output pointers 4-byte aligned,
+ * the size array 8-byte aligned — anything else is refused with code 1).  One kernel is launched on
  * `stream` (a cudaStream_t, NULL = default stream) and the call returns without waiting.
  * The first call on each device also looks up the array's device address — make that call
  * before starting any stream capture.  All calls share the array: calls that can overlap on

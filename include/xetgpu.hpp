@@ -8,6 +8,9 @@
 //     VerifyFile, VerifyFiles         <-> same names; a mismatch is an XetError with Code 6
 //     SetProgressHandler              <-> same name                           (xet.go:93-151)
 //     XetError{Code, Message, Details}<-> xet::XetError                       (xet.go:227-238, 507-522)
+//     XetFileChecksum, XetChecksumAlgorithm, XetChecksumMetadataKey <-> same names: the "xet" case of the replica
+//                                        agent's GetFileChecksum (internal/ome-agent/replica/replicator/helper.go:86-130)
+//     NewGpuMultiHasher / VerifyFiles  <-> xet::GpuMultiHasher: every GPU of the node from one process
 // Error behaviour follows the reference: every failure carries the reference's XetErrorCode
 // (pkg/xet/src/error.rs:12-23) plus message and details; nothing is computed on the CPU.
 #pragma once
@@ -23,6 +26,10 @@
 namespace xet {
 
 constexpr int ErrorCodeChecksumMismatch = XETGPU_ERR_CHECKSUM_MISMATCH;
+// Names the replica agent's ChecksumConfig / object metadata would use, next to "md5" / "sha256" and
+// "opc-meta-md5" / "opc-meta-sha256" (internal/ome-agent/replica/replicator/helper.go:28-31).
+constexpr const char* XetChecksumAlgorithm = "xet";
+constexpr const char* XetChecksumMetadataKey = "opc-meta-xet";
 
 struct XetError : std::runtime_error {
     int Code;
@@ -113,6 +120,11 @@ class GpuHasher {
         return d;
     }
 
+    // GetFileChecksum(filePath, "xet") of the replica agent (helper.go:86-109): path in, digest string out.
+    // The digest is the 64-hex-digit form the Hub advertises (md5/sha256 are base64 there; a Xet hash is
+    // compared with X-Xet-Hash, which is hex).
+    std::string XetFileChecksum(const std::string& filePath) { return HashFiles({filePath})[0].Hash; }
+
     // Returns normally on a match; throws XetError{Code 6} (expected and computed hash in Details) otherwise.
     void VerifyFile(const std::string& path, const std::string& expectedHex) {
         detail::check(xetgpu_verify_file(ctx_, path.c_str(), expectedHex.c_str()));
@@ -157,6 +169,65 @@ class GpuHasher {
 
     XetGpuContext* ctx_ = nullptr;
     ProgressHandler handler_;
+    std::vector<bool> verdicts_;
+};
+
+// GetFileChecksum with the reference's signature and error behaviour for the algorithm this library adds:
+// any other algorithm is "unsupported checksum algorithm: <name>" as in helper.go:95.
+inline std::string GetFileChecksum(GpuHasher& h, const std::string& filePath, const std::string& algorithm) {
+    if (algorithm != XetChecksumAlgorithm) throw std::invalid_argument("unsupported checksum algorithm: " + algorithm);
+    return h.XetFileChecksum(filePath);
+}
+
+// Every GPU of the node from one process (xetgpu_multi_*).
+class GpuMultiHasher {
+  public:
+    explicit GpuMultiHasher(const std::vector<int>& devices = {}) {  // NewGpuMultiHasher; empty = all visible devices
+        xetgpu_version_0_1_0();
+        std::vector<int32_t> d(devices.begin(), devices.end());
+        detail::check(xetgpu_multi_new(d.empty() ? nullptr : d.data(), d.size(), nullptr, &ctx_));
+    }
+    GpuMultiHasher(const GpuMultiHasher&) = delete;
+    GpuMultiHasher& operator=(const GpuMultiHasher&) = delete;
+    ~GpuMultiHasher() { Close(); }
+    void Close() {
+        if (ctx_) xetgpu_multi_free(ctx_);
+        ctx_ = nullptr;
+    }
+    size_t Devices() const { return xetgpu_multi_device_count(ctx_); }
+
+    std::vector<FileDigest> HashFiles(const std::vector<std::string>& paths) {
+        std::vector<const char*> cp;
+        for (const auto& p : paths) cp.push_back(p.c_str());
+        XetGpuResult* res = nullptr;
+        detail::check(xetgpu_multi_hash_files(ctx_, cp.data(), cp.size(), 0, nullptr, &res));
+        std::vector<FileDigest> out(paths.size());
+        for (size_t i = 0; i < paths.size(); i++)
+            out[i] = FileDigest{detail::hex(res->files[i].file_hash), detail::hex(res->files[i].merkle_root),
+                                res->files[i].size, res->files[i].n_chunks};
+        xetgpu_free_result(res);
+        return out;
+    }
+
+    // As GpuHasher::VerifyFiles.
+    std::vector<bool> VerifyFiles(const std::vector<std::string>& paths, const std::vector<std::string>& expectedHex) {
+        if (paths.size() != expectedHex.size()) throw XetError(XETGPU_ERR_INVALID_CONFIG, "paths and hashes differ in length", "");
+        std::vector<const char*> cp, ch;
+        for (size_t i = 0; i < paths.size(); i++) {
+            cp.push_back(paths[i].c_str());
+            ch.push_back(expectedHex[i].empty() ? nullptr : expectedHex[i].c_str());
+        }
+        std::vector<uint8_t> ok(paths.size() ? paths.size() : 1);
+        ::XetError* err = xetgpu_multi_verify_files(ctx_, cp.data(), ch.data(), paths.size(), nullptr, ok.data());
+        verdicts_.assign(paths.size(), false);
+        for (size_t i = 0; i < paths.size(); i++) verdicts_[i] = ok[i] != 0;
+        detail::check(err);
+        return verdicts_;
+    }
+    const std::vector<bool>& LastVerdicts() const { return verdicts_; }
+
+  private:
+    XetGpuMulti* ctx_ = nullptr;
     std::vector<bool> verdicts_;
 };
 

@@ -84,7 +84,11 @@ func (h *GpuHasher) SetProgressHandler(handler ProgressHandler, throttle time.Du
 		return nil, convertGpuError(cerr)
 	}
 	return func() {
-		C.xetgpu_context_set_progress_callback(h.ctx, nil, nil, 0)
+		if h.ctx != nil {
+			if cerr := C.xetgpu_context_set_progress_callback(h.ctx, nil, nil, 0); cerr != nil {
+				C.xetgpu_free_error(cerr)
+			}
+		}
 		handle.Delete()
 	}, nil
 }
@@ -107,14 +111,10 @@ func (h *GpuHasher) HashFiles(ctx context.Context, paths []string) ([]FileDigest
 			C.free(unsafe.Pointer(p))
 		}
 	}()
-	handle := cgo.NewHandle(ctx)
-	defer handle.Delete()
-	tok := C.XetCancellationToken{
-		callback:  (C.XetCancellationCallback)(C.goXetShouldCancel),
-		user_data: unsafe.Pointer(handle),
-	}
+	tok, release := cancelToken(ctx)
+	defer release()
 	var res *C.XetGpuResult
-	if cerr := C.xetgpu_hash_files(h.ctx, &cpaths[0], C.size_t(len(paths)), 0, &tok, &res); cerr != nil {
+	if cerr := C.xetgpu_hash_files(h.ctx, &cpaths[0], C.size_t(len(paths)), 0, tok, &res); cerr != nil {
 		return nil, convertGpuError(cerr)
 	}
 	defer C.xetgpu_free_result(res)
@@ -134,6 +134,9 @@ func (h *GpuHasher) HashFiles(ctx context.Context, paths []string) ([]FileDigest
 
 // HashBytes hashes one in-memory buffer.
 func (h *GpuHasher) HashBytes(b []byte) (FileDigest, error) {
+	if h.ctx == nil {
+		return FileDigest{}, errors.New("xet: hasher is closed")
+	}
 	offsets := [2]C.uint64_t{0, C.uint64_t(len(b))}
 	var p unsafe.Pointer
 	if len(b) > 0 {
@@ -153,6 +156,9 @@ func (h *GpuHasher) HashBytes(b []byte) (FileDigest, error) {
 // Code == ErrorCodeChecksumMismatch (expected and computed hashes in Details) when it does not.
 // Shape precedent: hub.VerifyChecksum (pkg/hfutil/hub/utils.go).
 func (h *GpuHasher) VerifyFile(path, expectedHex string) error {
+	if h.ctx == nil {
+		return errors.New("xet: hasher is closed")
+	}
 	cp, ce := C.CString(path), C.CString(expectedHex)
 	defer C.free(unsafe.Pointer(cp))
 	defer C.free(unsafe.Pointer(ce))
@@ -163,7 +169,13 @@ func (h *GpuHasher) VerifyFile(path, expectedHex string) error {
 // expected hash skips the file).  It returns the per-file verdicts; err is a *XetError with
 // Code == ErrorCodeChecksumMismatch when any file differs.
 func (h *GpuHasher) VerifyFiles(ctx context.Context, paths, expectedHex []string) ([]bool, error) {
+	if h.ctx == nil {
+		return nil, errors.New("xet: hasher is closed")
+	}
 	n := len(paths)
+	if len(expectedHex) != n {
+		return nil, &XetError{Code: 1, Message: "paths and expectedHex differ in length"}
+	}
 	if n == 0 {
 		return nil, nil
 	}
@@ -183,14 +195,114 @@ func (h *GpuHasher) VerifyFiles(ctx context.Context, paths, expectedHex []string
 			}
 		}
 	}()
-	handle := cgo.NewHandle(ctx)
-	defer handle.Delete()
-	tok := C.XetCancellationToken{
-		callback:  (C.XetCancellationCallback)(C.goXetShouldCancel),
-		user_data: unsafe.Pointer(handle),
-	}
+	tok, release := cancelToken(ctx)
+	defer release()
 	ok := make([]C.uint8_t, n)
-	err := convertGpuError(C.xetgpu_verify_files(h.ctx, &cp[0], &ch[0], C.size_t(n), &tok, &ok[0]))
+	err := convertGpuError(C.xetgpu_verify_files(h.ctx, &cp[0], &ch[0], C.size_t(n), tok, &ok[0]))
+	out := make([]bool, n)
+	for i := range ok {
+		out[i] = ok[i] != 0
+	}
+	return out, err
+}
+
+// cancelToken wraps ctx the way xet.go does for xet_download_file (xet.go:366-375): the reused bridge
+// goXetShouldCancel type-asserts *cancellationBridge, so the handle must carry exactly that type.
+// A nil or never-cancelled context yields a nil token.
+func cancelToken(ctx context.Context) (*C.XetCancellationToken, func()) {
+	if ctx == nil || ctx.Done() == nil {
+		return nil, func() {}
+	}
+	handle := cgo.NewHandle(&cancellationBridge{ctx: ctx})
+	tok := (*C.XetCancellationToken)(C.malloc(C.size_t(unsafe.Sizeof(C.XetCancellationToken{}))))
+	tok.callback = (C.XetCancellationCallback)(C.goXetShouldCancel)
+	tok.user_data = unsafe.Pointer(handle)
+	return tok, func() {
+		C.free(unsafe.Pointer(tok))
+		handle.Delete()
+	}
+}
+
+// XetChecksumMetadataKey is the object-metadata key the replica agent would store the digest under, next to
+// OCIObjectMD5MetadataKey / OCIObjectSHA256MetadataKey (internal/ome-agent/replica/replicator/helper.go:28-31).
+const XetChecksumMetadataKey = "opc-meta-xet"
+
+// XetFileChecksum has the shape of replicator.GetFileChecksum(filePath, algorithm) for algorithm "xet"
+// (internal/ome-agent/replica/replicator/helper.go:86-109): path in, digest string out.  md5/sha256 are
+// base64 of the raw digest there; the Xet digest is returned in the form every other Xet tool prints and
+// the Hub advertises (64 hex digits, MerkleHash::hex), so that it can be compared with X-Xet-Hash directly.
+func (h *GpuHasher) XetFileChecksum(filePath string) (string, error) {
+	d, err := h.HashFiles(context.Background(), []string{filePath})
+	if err != nil {
+		return "", err
+	}
+	return d[0].Hash, nil
+}
+
+// GpuMultiHasher owns one libxetgpu context per listed GPU (xetgpu_multi_*): the form a single
+// model-agent process (cmd/model-agent/main.go:243-271) uses to reach every GPU of its node.
+type GpuMultiHasher struct {
+	ctx *C.XetGpuMulti
+}
+
+// NewGpuMultiHasher creates contexts on the given CUDA devices (nil = every visible device).
+func NewGpuMultiHasher(devices []int) (*GpuMultiHasher, error) {
+	var ctx *C.XetGpuMulti
+	var dp *C.int32_t
+	cdev := make([]C.int32_t, len(devices))
+	for i, d := range devices {
+		cdev[i] = C.int32_t(d)
+	}
+	if len(cdev) > 0 {
+		dp = &cdev[0]
+	}
+	if cerr := C.xetgpu_multi_new(dp, C.size_t(len(cdev)), nil, &ctx); cerr != nil {
+		return nil, convertGpuError(cerr)
+	}
+	return &GpuMultiHasher{ctx: ctx}, nil
+}
+
+// Close releases every per-device context.
+func (m *GpuMultiHasher) Close() error {
+	if m.ctx != nil {
+		C.xetgpu_multi_free(m.ctx)
+		m.ctx = nil
+	}
+	return nil
+}
+
+// VerifyFiles is (*GpuHasher).VerifyFiles over all devices of the node.
+func (m *GpuMultiHasher) VerifyFiles(ctx context.Context, paths, expectedHex []string) ([]bool, error) {
+	if m.ctx == nil {
+		return nil, errors.New("xet: hasher is closed")
+	}
+	n := len(paths)
+	if len(expectedHex) != n {
+		return nil, &XetError{Code: 1, Message: "paths and expectedHex differ in length"}
+	}
+	if n == 0 {
+		return nil, nil
+	}
+	cp := make([]*C.char, n)
+	ch := make([]*C.char, n)
+	for i := range paths {
+		cp[i] = C.CString(paths[i])
+		if expectedHex[i] != "" {
+			ch[i] = C.CString(expectedHex[i])
+		}
+	}
+	defer func() {
+		for i := range cp {
+			C.free(unsafe.Pointer(cp[i]))
+			if ch[i] != nil {
+				C.free(unsafe.Pointer(ch[i]))
+			}
+		}
+	}()
+	tok, release := cancelToken(ctx)
+	defer release()
+	ok := make([]C.uint8_t, n)
+	err := convertGpuError(C.xetgpu_multi_verify_files(m.ctx, &cp[0], &ch[0], C.size_t(n), tok, &ok[0]))
 	out := make([]bool, n)
 	for i := range ok {
 		out[i] = ok[i] != 0

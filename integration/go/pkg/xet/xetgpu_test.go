@@ -44,3 +44,47 @@ func TestGpuHasherGolden(t *testing.T) {
 		}
 	}
 }
+
+// A cancelled context must reach the library: the bridge reused from xet.go type-asserts *cancellationBridge
+// (xet.go:68-85), which is what cancelToken wraps the context in.
+func TestGpuHasherCancellation(t *testing.T) {
+	h, err := NewGpuHasher(-1)
+	if err != nil {
+		t.Skipf("no B200 available: %v", err)
+	}
+	defer h.Close()
+	p := filepath.Join(t.TempDir(), "big")
+	if err := os.WriteFile(p, make([]byte, 64<<20), 0o600); err != nil {
+		t.Fatal(err)
+	}
+	ctx, cancel := context.WithCancel(context.Background())
+	cancel()
+	if _, err := h.HashFiles(ctx, []string{p}); err == nil {
+		t.Fatal("expected a cancellation error")
+	} else if xe, ok := err.(*XetError); !ok || xe.Code != 7 {
+		t.Fatalf("expected XetError code 7 (Cancelled), got %v", err)
+	}
+	if _, err := h.VerifyFiles(ctx, []string{p}, []string{"00"}); err == nil {
+		t.Fatal("expected an error")
+	}
+}
+
+// The replica agent's GetFileChecksum shape for algorithm "xet".
+func TestXetFileChecksum(t *testing.T) {
+	h, err := NewGpuHasher(-1)
+	if err != nil {
+		t.Skipf("no B200 available: %v", err)
+	}
+	defer h.Close()
+	p := filepath.Join(t.TempDir(), "hello")
+	if err := os.WriteFile(p, []byte("hello world"), 0o600); err != nil {
+		t.Fatal(err)
+	}
+	got, err := h.XetFileChecksum(p)
+	if err != nil || got != "f15edd43b7e85cfd25e2758ffe13b99fdd09dfa817e8d9f6548722a7a126db7f" {
+		t.Fatalf("got %q, %v", got, err)
+	}
+	if XetChecksumAlgorithm != "xet" || XetChecksumMetadataKey != "opc-meta-xet" {
+		t.Fatal("constants changed")
+	}
+}

@@ -224,6 +224,12 @@ extern "C" XetError* xetgpu_merkle_from_chunks_static(const uint8_t* device_chun
         return static_error(XETGPU_ERR_INVALID_CONFIG,
                             "chunk list too long for the static-scratch entry point; use xetgpu_merkle_from_chunks", buf);
     }
+    // The kernel moves hashes as 32-bit words and sizes as 64-bit words; a pointer into the middle of a packed
+    // record would fault on the device, and such a fault is sticky for the whole process, so refuse it here.
+    if (((uintptr_t)device_chunk_hashes | (uintptr_t)device_out_merkle_root | (uintptr_t)device_out_file_hash) & 3u ||
+        ((uintptr_t)device_chunk_sizes & 7u))
+        return static_error(XETGPU_ERR_INVALID_CONFIG,
+                            "misaligned pointer: hashes and outputs must be 4-byte aligned, sizes 8-byte aligned", nullptr);
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return static_error(XETGPU_ERR_UNKNOWN, "cudaGetDevice failed", cudaGetErrorString(e));

@@ -145,6 +145,7 @@ def merkle_from_chunks_static(hashes_dev_ptr: int, sizes_dev_ptr: int, n_chunks:
 
     For callers that may not allocate on the GPU (memory owned by another allocator, latency
     paths, no XetGpuContext at hand).  All five pointers are device addresses the caller owns;
+    hash and output pointers 4-byte aligned, the size array 8-byte aligned;
     at most STATIC_MERKLE_MAX_CHUNKS chunks; the kernel is only enqueued on `stream` — synchronise
     before reading the outputs, and do not let two calls overlap on the GPU (they share one
     fixed scratch array inside the library).

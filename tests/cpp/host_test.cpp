@@ -89,7 +89,39 @@ int main(int argc, char** argv) {
         } catch (const xet::XetError& e) {
             EXPECT(e.Code == XETGPU_ERR_INVALID_CONFIG);
         }
+        // the "xet" case of the replica agent's GetFileChecksum: path + algorithm in, digest string out
+        EXPECT(xet::GetFileChecksum(h, paths[1], xet::XetChecksumAlgorithm) == cases[1].hash);
+        EXPECT(h.XetFileChecksum(paths[4]) == cases[4].hash);
+        EXPECT(std::string(xet::XetChecksumMetadataKey) == "opc-meta-xet");
+        try {
+            xet::GetFileChecksum(h, paths[1], "crc32");
+            EXPECT(false);
+        } catch (const std::invalid_argument& e) {
+            EXPECT(std::string(e.what()) == "unsupported checksum algorithm: crc32");
+        }
+        try {
+            h.XetFileChecksum(dir + "/does-not-exist");
+            EXPECT(false);
+        } catch (const xet::XetError& e) {
+            EXPECT(e.Code == XETGPU_ERR_NOT_FOUND);
+        }
         h.Close();
+        // the node-wide hasher a single model-agent process would hold (all visible GPUs)
+        xet::GpuMultiHasher m;
+        EXPECT(m.Devices() >= 1);
+        for (size_t i = 0; i < cases.size(); i++) hashes[i] = cases[i].hash;
+        auto md = m.HashFiles(paths);
+        for (size_t i = 0; i < cases.size(); i++) EXPECT(md[i].Hash == cases[i].hash);
+        auto mok = m.VerifyFiles(paths, hashes);
+        EXPECT(mok.size() == cases.size() && mok[0] && mok[3]);
+        hashes[3] = std::string(64, '1');
+        try {
+            m.VerifyFiles(paths, hashes);
+            EXPECT(false);
+        } catch (const xet::XetError& e) {
+            EXPECT(xet::IsChecksumMismatch(e) && !m.LastVerdicts()[3] && m.LastVerdicts()[4]);
+        }
+        m.Close();
     } catch (const xet::XetError& e) {
         std::fprintf(stderr, "unexpected: %s\n", e.what());
         return 2;

@@ -442,3 +442,19 @@ def test_cpp_host_mirror(tmp_path):
     r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.startswith("ok")
+
+
+def test_reference_fixture_files_on_gpu(hasher):
+    """The reference's own safetensors fixtures (pkg/hfutil/modelconfig/testdata/tiny-random-PhiModel), shipped as
+    bytes under tests/golden/reference_fixtures (model-1-of-2 and model-2-of-2 are byte-identical), hashed by the GPU
+    path through xetgpu_hash_files and compared with the hf_xet hashes recorded in the golden file."""
+    fix = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_fixtures")
+    exp = GOLDEN["reference_fixture_files"]
+    base = "pkg/hfutil/modelconfig/testdata/tiny-random-PhiModel/"
+    paths = [os.path.join(fix, "model-1-of-2.safetensors"), os.path.join(fix, "config.json")]
+    cl = hasher.hash_files(paths, want_chunks=True)
+    assert cl.files[0].hex == exp[base + "model-1-of-2.safetensors"]["file_hash"] == exp[base + "model-2-of-2.safetensors"]["file_hash"]
+    assert cl.files[1].hex == exp[base + "config.json"]["file_hash"]
+    assert cl.files[0].size == exp[base + "model-1-of-2.safetensors"]["n"]
+    for f, p in enumerate(paths):
+        check_against_oracle(cl, f, np.fromfile(p, dtype=np.uint8))
