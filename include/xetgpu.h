@@ -116,6 +116,7 @@ enum {
  * binding does the latter for torch tensors (ome_b200/hasher.py, _order_after_torch). */
 
 #define XETGPU_WANT_CHUNKS 1u /* also return per-chunk end offsets and hashes */
+#define XETGPU_WANT_XORBS 2u  /* also form xorbs and return one hash per xorb (see XetGpuXorb) */
 
 /* One file's result.  Hash bytes are in RAW DIGEST ORDER; the Xet hex form
  * (MerkleHash::hex, four LE u64 words as %016x) is produced by xetgpu_hash_to_hex. */
@@ -127,12 +128,27 @@ typedef struct {
     uint64_t first_chunk;    /* index of this file's first chunk in XetGpuResult.chunk_* */
 } XetGpuFileResult;
 
+/* One xorb: the unit xet-core's upload side stores in the CAS.  A file's chunks are packed, in
+ * order, into xorbs of at most 64 MiB of chunk bytes and at most 8192 chunks; `hash` is merklehash::xorb_hash =
+ * aggregated_node_hash over the xorb's (chunk hash, length) list.  The hash FUNCTION is pinned through the file hash;
+ * the GROUPING is parity-unpinned (hf_xet.hash_files does not expose xorbs, and a real upload also drops chunks
+ * that deduplicate against earlier xorbs): this is the no-dedup, one-file-at-a-time policy. */
+typedef struct {
+    uint8_t hash[32];        /* raw digest order */
+    uint64_t file;           /* index of the file in this result */
+    uint64_t first_chunk;    /* index of the xorb's first chunk WITHIN its file */
+    uint64_t n_chunks;
+    uint64_t bytes;          /* sum of the chunk lengths */
+} XetGpuXorb;
+
 typedef struct {
     size_t n_files;
     XetGpuFileResult* files;
     uint64_t n_chunks;       /* 0 unless XETGPU_WANT_CHUNKS */
     uint64_t* chunk_ends;    /* per chunk: exclusive end offset, relative to its own file */
     uint8_t* chunk_hashes;   /* 32 bytes per chunk, raw digest order */
+    uint64_t n_xorbs;        /* 0 unless XETGPU_WANT_XORBS (fields added in 0.2.0, at the end of the struct) */
+    XetGpuXorb* xorbs;       /* sorted by file, then by first_chunk */
 } XetGpuResult;
 
 /* Device time of each stage of the last hash call, in milliseconds (CUDA events on the
@@ -154,7 +170,7 @@ typedef struct {
 } XetGpuTimings;
 
 /* Link-time version guard, same idea as xet_version_1_0_0 [pkg/xet/xet.h:94]. */
-extern void xetgpu_version_0_1_0(void);
+extern void xetgpu_version_0_2_0(void);
 
 /* Context lifecycle — shaped like xet_client_new / xet_client_free [pkg/xet/xet.h:97-98],
  * but returns an error object instead of a bare NULL so CUDA failures are reportable. */
@@ -300,6 +316,50 @@ XetError* xetgpu_multi_hash_files(XetGpuMulti* ctx, const char* const* paths, si
                                   const XetCancellationToken* cancel_token, XetGpuResult** out_result);
 XetError* xetgpu_multi_verify_files(XetGpuMulti* ctx, const char* const* paths, const char* const* expected_hex,
                                     size_t n_files, const XetCancellationToken* cancel_token, uint8_t* out_ok);
+
+/* ---- safetensors-aware ingestion ---------------------------------------------------
+ * The shard header as OME's model-config parser reads it [pkg/hfutil/modelconfig/safetensors.go:67-141]: u64-LE
+ * header length (at most 10 MB), JSON object of tensor name -> {dtype, shape, data_offsets}, "__metadata__" skipped.
+ * parameter_count is what modelconfig.ParseSafetensors returns (product of every non-empty shape, same overflow and
+ * invalid-dimension errors, same message texts); the tensor table adds what a partitioner needs: each tensor's
+ * absolute byte extent in the file, ascending.  Errors: code 4 / 8 for open / short-read failures, code 1 for a
+ * malformed header. */
+typedef struct {
+    const char* name;      /* owned by the index */
+    const char* dtype;
+    uint64_t begin, end;   /* byte extent in the file: 8 + header_len + data_offsets */
+    uint64_t n_elements;   /* product of the shape; 0 for an empty shape */
+    uint32_t rank;
+} XetGpuTensorInfo;
+
+typedef struct {
+    uint64_t file_size;    /* 0 if unknown (xetgpu_safetensors_parse without a size) */
+    uint64_t header_len;
+    uint64_t data_start;   /* 8 + header_len */
+    uint64_t n_tensors;
+    XetGpuTensorInfo* tensors;  /* ascending by begin */
+    int64_t parameter_count;
+} XetGpuSafetensorsIndex;
+
+XetError* xetgpu_safetensors_open(const char* path, XetGpuSafetensorsIndex** out_index);
+/* `head` = the first head_len bytes of a shard (at least 8 + header length of them). */
+XetError* xetgpu_safetensors_parse(const void* head, uint64_t head_len, uint64_t file_size,
+                                   XetGpuSafetensorsIndex** out_index);
+void xetgpu_safetensors_free(XetGpuSafetensorsIndex* index);
+/* Byte ranges for n_ranges owners of one shard with interior bounds on tensor boundaries (nearest tensor begin / end
+ * within a quarter range of the equal split; the 4096-aligned equal split itself when one tensor is larger than
+ * that).  out_bounds: n_ranges + 1 ascending offsets, [0] = 0, [n_ranges] = file_size; every non-empty interior
+ * range keeps at least XETGPU_RANGE_LEAD + 4096 bytes, so the ranges are valid inputs to xetgpu_hash_range. */
+XetError* xetgpu_safetensors_split(const XetGpuSafetensorsIndex* index, uint64_t file_size, size_t n_ranges,
+                                   uint64_t* out_bounds);
+/* Flag for xetgpu_multi_hash_files / _verify_files is implied: a *.safetensors file that is shared between devices
+ * has its in-file boundaries moved to the nearest tensor boundary (same quarter-range rule) unless
+ * XETGPU_NO_TENSOR_SNAP is passed.  Hashes do not depend on where the boundaries fall. */
+#define XETGPU_NO_TENSOR_SNAP 4u
+/* The byte ranges xetgpu_multi_hash_files would give each device for these files: up to `cap` rows of four u64
+ * (device index, file index, begin, end) in device order; *out_count = rows the plan has.  Tooling and tests. */
+XetError* xetgpu_multi_plan(XetGpuMulti* ctx, const char* const* paths, size_t n_files, uint32_t flags,
+                            uint64_t* out_pieces, size_t cap, size_t* out_count);
 
 /* K0: fill device memory with the SURVEY.md §8(d) counter-based splitmix64 stream:
  * dst[i] = byte (byte_off + i) of stream `seed`.  Benchmarks and tests only. */

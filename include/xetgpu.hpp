@@ -74,7 +74,7 @@ inline std::string hex(const uint8_t h[32]) {
 class GpuHasher {
   public:
     explicit GpuHasher(int device = -1) {  // NewGpuHasher
-        xetgpu_version_0_1_0();
+        xetgpu_version_0_2_0();
         XetGpuConfig cfg;
         std::memset(&cfg, 0, sizeof cfg);
         cfg.device = device;
@@ -183,7 +183,7 @@ inline std::string GetFileChecksum(GpuHasher& h, const std::string& filePath, co
 class GpuMultiHasher {
   public:
     explicit GpuMultiHasher(const std::vector<int>& devices = {}) {  // NewGpuMultiHasher; empty = all visible devices
-        xetgpu_version_0_1_0();
+        xetgpu_version_0_2_0();
         std::vector<int32_t> d(devices.begin(), devices.end());
         detail::check(xetgpu_multi_new(d.empty() ? nullptr : d.data(), d.size(), nullptr, &ctx_));
     }

@@ -14,8 +14,8 @@ package xet
 #include "xetgpu.h"
 
 // Link-time version check (same idiom as xet_version_1_0_0 in xet.go)
-extern void xetgpu_version_0_1_0(void);
-static void (*xetgpu_version_check)(void) = &xetgpu_version_0_1_0;
+extern void xetgpu_version_0_2_0(void);
+static void (*xetgpu_version_check)(void) = &xetgpu_version_0_2_0;
 
 // Existing Go callback bridges exported from xet.go
 extern void goXetProgressCallback(XetProgressUpdate* update, void* user_data);

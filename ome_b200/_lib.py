@@ -39,9 +39,25 @@ class XetGpuFileResult(C.Structure):
                 ("n_chunks", C.c_uint64), ("first_chunk", C.c_uint64)]
 
 
+class XetGpuXorb(C.Structure):
+    _fields_ = [("hash", C.c_uint8 * 32), ("file", C.c_uint64), ("first_chunk", C.c_uint64), ("n_chunks", C.c_uint64),
+                ("bytes", C.c_uint64)]
+
+
 class XetGpuResult(C.Structure):
     _fields_ = [("n_files", C.c_size_t), ("files", C.POINTER(XetGpuFileResult)), ("n_chunks", C.c_uint64),
-                ("chunk_ends", C.POINTER(C.c_uint64)), ("chunk_hashes", C.POINTER(C.c_uint8))]
+                ("chunk_ends", C.POINTER(C.c_uint64)), ("chunk_hashes", C.POINTER(C.c_uint8)),
+                ("n_xorbs", C.c_uint64), ("xorbs", C.POINTER(XetGpuXorb))]
+
+
+class XetGpuTensorInfo(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("dtype", C.c_char_p), ("begin", C.c_uint64), ("end", C.c_uint64),
+                ("n_elements", C.c_uint64), ("rank", C.c_uint32)]
+
+
+class XetGpuSafetensorsIndex(C.Structure):
+    _fields_ = [("file_size", C.c_uint64), ("header_len", C.c_uint64), ("data_start", C.c_uint64),
+                ("n_tensors", C.c_uint64), ("tensors", C.POINTER(XetGpuTensorInfo)), ("parameter_count", C.c_int64)]
 
 
 class XetGpuTimings(C.Structure):
@@ -57,7 +73,7 @@ CTX = C.c_void_p
 
 # name -> (restype, argtypes); mirrors include/xetgpu.h one to one
 SIGNATURES = {
-    "xetgpu_version_0_1_0": (None, []),
+    "xetgpu_version_0_2_0": (None, []),
     "xetgpu_context_new": (ERRP, [C.POINTER(XetGpuConfig), C.POINTER(CTX)]),
     "xetgpu_context_free": (None, [CTX]),
     "xetgpu_context_set_progress_callback": (ERRP, [CTX, ProgressCallback, C.c_void_p, C.c_uint32]),
@@ -89,6 +105,12 @@ SIGNATURES = {
                                        C.POINTER(XetCancellationToken), C.POINTER(C.POINTER(XetGpuResult))]),
     "xetgpu_multi_verify_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.c_size_t,
                                          C.POINTER(XetCancellationToken), C.POINTER(C.c_uint8)]),
+    "xetgpu_multi_plan": (ERRP, [CTX, C.POINTER(C.c_char_p), C.c_size_t, C.c_uint32, C.POINTER(C.c_uint64), C.c_size_t,
+                                 C.POINTER(C.c_size_t)]),
+    "xetgpu_safetensors_open": (ERRP, [C.c_char_p, C.POINTER(C.POINTER(XetGpuSafetensorsIndex))]),
+    "xetgpu_safetensors_parse": (ERRP, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.POINTER(XetGpuSafetensorsIndex))]),
+    "xetgpu_safetensors_free": (None, [C.POINTER(XetGpuSafetensorsIndex)]),
+    "xetgpu_safetensors_split": (ERRP, [C.POINTER(XetGpuSafetensorsIndex), C.c_uint64, C.c_size_t, C.POINTER(C.c_uint64)]),
     "xetgpu_fill_splitmix": (ERRP, [CTX, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
     "xetgpu_last_timings": (ERRP, [CTX, C.POINTER(XetGpuTimings)]),
     "xetgpu_free_error": (None, [ERRP]),

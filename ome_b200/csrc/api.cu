@@ -18,6 +18,7 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -67,7 +68,7 @@ extern "C" void xetgpu_free_error(XetError* err) {
     free(err);
 }
 
-extern "C" void xetgpu_version_0_1_0(void) {}
+extern "C" void xetgpu_version_0_2_0(void) {}
 
 // ----------------------------------------------------------------------------------- context
 struct Arena {
@@ -355,6 +356,8 @@ struct Plan {
     std::vector<uint64_t> slot_off;  // host prefix
     std::vector<uint64_t> seg_off;   // host prefix of per-file segment counts (K2)
     uint64_t n_segs = 0;
+    std::vector<uint64_t> xorb_off;  // host prefix of per-file xorb upper bounds (only with want_xorbs)
+    uint64_t n_xorb_slots = 0;
 };
 
 static uint32_t bit_length(uint64_t v) {
@@ -366,8 +369,19 @@ static uint32_t bit_length(uint64_t v) {
     return n;
 }
 
-static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, uint64_t cand_cap_hint) {
+static Plan make_plan(const uint64_t* offsets, size_t n_files, uint64_t total, uint64_t cand_cap_hint,
+                      bool want_xorbs = false) {
     Plan p;
+    if (want_xorbs) {  // a xorb other than a file's last holds more than 64 MiB - 128 KiB
+        p.xorb_off.resize(n_files + 1);
+        uint64_t x = 0;
+        for (size_t f = 0; f < n_files; f++) {
+            p.xorb_off[f] = x;
+            x += (offsets[f + 1] - offsets[f]) / (kMaxXorbBytes - kMaxChunk) + 2;
+        }
+        p.xorb_off[n_files] = x;
+        p.n_xorb_slots = x;
+    }
     p.total = total;
     p.n_files = (uint32_t)n_files;
     p.slot_off.resize(n_files + 1);
@@ -451,6 +465,19 @@ static XetError* carve(Lane* l, const Plan& p, PipelineBuffers* b, bool dry, uin
     b->file_hash = a.take<uint8_t>((F + 1) * 32);
     b->out_end = a.take<uint64_t>(S + 1);
     b->out_hash = a.take<uint8_t>((S + 1) * 32);
+    b->n_xorb_slots = p.n_xorb_slots;
+    if (p.n_xorb_slots) {
+        const uint64_t X = p.n_xorb_slots;
+        b->xorb_slot_off = a.take<uint64_t>(F + 1);
+        b->xorb_count = a.take<uint32_t>(F + 1);
+        b->xorb_node_off = a.take<uint64_t>(X + 1);
+        b->xorb_n = a.take<uint32_t>(X + 1);
+        b->xorb_bytes = a.take<uint64_t>(X + 1);
+        b->xorb_root = a.take<uint8_t>((X + 1) * 32);
+        b->xorb_scratch = a.take<uint8_t>((X + 1) * 32);
+        b->xorb_level[0] = a.take<uint32_t>(X + 1);
+        b->xorb_level[1] = a.take<uint32_t>(X + 1);
+    }
     b->scan_partial = a.take<uint64_t>(scan_blocks(std::max<uint64_t>(std::max<uint64_t>(std::max<uint64_t>(T, S), F), G) + 2) + 1);
     b->scalars = a.take<uint64_t>(8);
     *need = a.used;
@@ -671,6 +698,7 @@ extern "C" void xetgpu_free_result(XetGpuResult* r) {
     free(r->files);
     free(r->chunk_ends);
     free(r->chunk_hashes);
+    free(r->xorbs);
     free(r);
 }
 
@@ -680,6 +708,7 @@ struct RunOptions {
     const RangeWalk* range = nullptr;  // byte-range mode (one file)
     uint64_t end_bias = 0;             // added to every returned chunk end (range mode: file position of data[0])
     bool want_chunks = false;
+    bool want_xorbs = false;           // also form xorbs (greedy <= 64 MiB / <= 8192 chunks) and hash each one
     bool resolve_only = false;         // stop after K2 (range exit-cut query)
     uint64_t* exit_cut_abs = nullptr;  // resolve_only / range: last cut (absolute in data), or walk_start if none
     bool skip_merkle = false;
@@ -699,6 +728,12 @@ struct GroupState {
     uint32_t* h_count = nullptr;
     uint8_t* h_hash = nullptr;
     uint8_t* h_root = nullptr;
+    // xorb readback (want_xorbs)
+    uint32_t* h_xcount = nullptr;
+    uint64_t* h_xoff = nullptr;
+    uint64_t* h_xbytes = nullptr;
+    uint32_t* h_xn = nullptr;
+    uint8_t* h_xroot = nullptr;
 };
 
 // Enqueue the whole pipeline for one group on `lane` (no host synchronisation).
@@ -710,7 +745,8 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
     const uint64_t total = n_files ? offsets[n_files] : 0;
     g->total = total;
     g->n_files = n_files;
-    g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint);
+    const bool xorbs = opt.want_xorbs && !opt.resolve_only && !opt.skip_merkle;
+    g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint, xorbs);
     const Plan& plan = g->plan;
     PipelineBuffers& b = g->b;
     b = PipelineBuffers{};
@@ -720,7 +756,9 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
         for (int i = 0; i < 4; i++) b.ev_kernel[i] = lane->ev_kernel[i];
     // metadata upload through pinned memory
     const uint64_t F = n_files;
-    const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256;
+    const uint64_t X = plan.n_xorb_slots;
+    const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256 +
+                                (xorbs ? (F + 1) * 8 + (F + 2) * 4 + (X + 1) * (8 + 8 + 4 + 32) + 64 : 0);
     if (XetError* e = ensure_meta(lane, meta_bytes)) return e;
     uint64_t* h_off = reinterpret_cast<uint64_t*>(lane->h_meta);
     uint64_t* h_slot = h_off + (F + 1);
@@ -751,6 +789,12 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
         launches += launch_gather(b, st);
         if (timing) cudaEventRecord(lane->ev[3], st);
         if (!opt.skip_merkle) launches += launch_merkle(b, st);
+        if (xorbs && X) {
+            uint64_t* h_xs = reinterpret_cast<uint64_t*>(lane->h_meta + meta_bytes - (F + 1) * 8 - 8);  // upload area (tail of the block)
+            memcpy(h_xs, plan.xorb_off.data(), (F + 1) * 8);
+            CU(cudaMemcpyAsync((void*)b.xorb_slot_off, h_xs, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+            launches += launch_xorbs(b, st);
+        }
         if (timing) cudaEventRecord(lane->ev[4], st);
     } else {
         launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
@@ -777,6 +821,20 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
             CU(cudaMemcpyAsync(g->h_root, b.file_root, F * 32, cudaMemcpyDeviceToHost, st));
         }
     }
+    if (xorbs && X) {
+        uint8_t* p = g->h_root + (F + 1) * 32;
+        p += (8 - ((uintptr_t)p & 7)) & 7;
+        g->h_xoff = reinterpret_cast<uint64_t*>(p);
+        g->h_xbytes = g->h_xoff + (X + 1);
+        g->h_xn = reinterpret_cast<uint32_t*>(g->h_xbytes + (X + 1));
+        g->h_xcount = g->h_xn + (X + 1);
+        g->h_xroot = reinterpret_cast<uint8_t*>(g->h_xcount + (F + 2));
+        CU(cudaMemcpyAsync(g->h_xoff, b.xorb_node_off, X * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(g->h_xbytes, b.xorb_bytes, X * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(g->h_xn, b.xorb_n, X * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(g->h_xcount, b.xorb_count, F * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(g->h_xroot, b.xorb_root, X * 32, cudaMemcpyDeviceToHost, st));
+    }
     if (timing) cudaEventRecord(lane->ev[5], st);
     g->launches = launches;
     return nullptr;
@@ -787,6 +845,7 @@ struct ResultBuilder {
     std::vector<XetGpuFileResult> files;
     std::vector<uint64_t> ends;
     std::vector<uint8_t> hashes;
+    std::vector<XetGpuXorb> xorbs;
     uint64_t n_cand = 0;
     int launches = 0;
     float gear_ms = 0, resolve_ms = 0, blake3_ms = 0, merkle_ms = 0, d2h_ms = 0, gear_kernel_ms = 0, leaf_kernel_ms = 0,
@@ -828,6 +887,20 @@ static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const
         fr.n_chunks = g->h_count[f];
         fr.first_chunk = (opt.want_chunks ? chunk0 : 0) + g->h_base[f];
         rb->files.push_back(fr);
+    }
+    if (g->h_xcount) {
+        const size_t file0 = rb->files.size() - F;
+        for (size_t f = 0; f < F; f++)
+            for (uint32_t k = 0; k < g->h_xcount[f]; k++) {
+                const uint64_t sx = plan.xorb_off[f] + k;
+                XetGpuXorb xo{};
+                memcpy(xo.hash, g->h_xroot + sx * 32, 32);
+                xo.file = file0 + f;
+                xo.first_chunk = g->h_xoff[sx] - g->h_base[f];  // file-relative chunk index
+                xo.n_chunks = g->h_xn[sx];
+                xo.bytes = g->h_xbytes[sx];
+                rb->xorbs.push_back(xo);
+            }
     }
     if (opt.want_chunks && n_chunks) {
         rb->ends.resize(chunk0 + n_chunks);
@@ -903,6 +976,15 @@ static XetError* build_result(const ResultBuilder& rb, bool want_chunks, XetGpuR
         }
         memcpy(r->chunk_ends, rb.ends.data(), rb.ends.size() * 8);
         memcpy(r->chunk_hashes, rb.hashes.data(), rb.hashes.size());
+    }
+    if (!rb.xorbs.empty()) {
+        r->n_xorbs = rb.xorbs.size();
+        r->xorbs = (XetGpuXorb*)malloc(rb.xorbs.size() * sizeof(XetGpuXorb));
+        if (!r->xorbs) {
+            xetgpu_free_result(r);
+            return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+        }
+        memcpy(r->xorbs, rb.xorbs.data(), rb.xorbs.size() * sizeof(XetGpuXorb));
     }
     *out_result = r;
     return nullptr;
@@ -1129,6 +1211,7 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
     }
     RunOptions opt;
     opt.want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
+    opt.want_xorbs = (flags & XETGPU_WANT_XORBS) != 0;
     return run_batch(c, d, host, rel.data(), n_files, opt, out_result);
 }
 
@@ -1211,7 +1294,8 @@ struct FileChunks {
 
 static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, const std::vector<size_t>& idx,
                                   const std::vector<uint64_t>& sizes, bool want_chunks, const XetCancellationToken* cancel,
-                                  FileProgress* prog, XetGpuFileResult* files_out, std::vector<FileChunks>* chunks_out) {
+                                  FileProgress* prog, XetGpuFileResult* files_out, std::vector<FileChunks>* chunks_out,
+                                  std::vector<XetGpuXorb>* xorbs_out = nullptr) {
     uint64_t bytes_before = 0;
     size_t k0 = 0;
     while (k0 < idx.size()) {
@@ -1236,8 +1320,14 @@ static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, co
         }
         RunOptions opt;
         opt.want_chunks = want_chunks;
+        opt.want_xorbs = xorbs_out != nullptr;
         XetGpuResult* part = nullptr;
         if (XetError* e = run_pipeline(c, c->d_input, rel.data(), k1 - k0, opt, &part)) return e;
+        for (uint64_t x = 0; xorbs_out && x < part->n_xorbs; x++) {
+            XetGpuXorb xo = part->xorbs[x];
+            xo.file = idx[k0 + xo.file];
+            xorbs_out->push_back(xo);
+        }
         for (size_t k = k0; k < k1; k++) {
             const XetGpuFileResult& fr = part->files[k - k0];
             files_out[idx[k]] = fr;
@@ -1255,7 +1345,7 @@ static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, co
 
 // Per-file results + per-file chunk vectors -> one XetGpuResult (files in caller order, chunks file by file).
 static XetError* assemble_result(std::vector<XetGpuFileResult>& files, std::vector<FileChunks>& chunks, bool want_chunks,
-                                 XetGpuResult** out_result) {
+                                 XetGpuResult** out_result, const std::vector<XetGpuXorb>* xorbs = nullptr) {
     XetGpuResult* total = (XetGpuResult*)calloc(1, sizeof(XetGpuResult));
     if (!total) return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
     total->n_files = files.size();
@@ -1287,6 +1377,16 @@ static XetError* assemble_result(std::vector<XetGpuFileResult>& files, std::vect
             w += fc.ends.size();
         }
     }
+    if (xorbs && !xorbs->empty()) {
+        total->n_xorbs = xorbs->size();
+        total->xorbs = (XetGpuXorb*)malloc(xorbs->size() * sizeof(XetGpuXorb));
+        if (!total->xorbs) {
+            xetgpu_free_result(total);
+            return make_error(XETGPU_ERR_UNKNOWN, "out of host memory");
+        }
+        memcpy(total->xorbs, xorbs->data(), xorbs->size() * sizeof(XetGpuXorb));
+        // batches complete in caller order, so the list is already sorted by file
+    }
     *out_result = total;
     return nullptr;
 }
@@ -1315,12 +1415,14 @@ extern "C" XetError* xetgpu_hash_files(XetGpuContext* c, const char* const* path
     for (size_t f = 0; f < n_files; f++) idx[f] = f;
     std::vector<XetGpuFileResult> files(n_files);
     std::vector<FileChunks> chunks(want_chunks ? n_files : 0);
+    const bool want_xorbs = (flags & XETGPU_WANT_XORBS) != 0;
+    std::vector<XetGpuXorb> xorbs;
     if (XetError* e = hash_whole_files(c, paths, idx, sizes, want_chunks, cancel, &prog, files.data(),
-                                       want_chunks ? &chunks : nullptr)) {
+                                       want_chunks ? &chunks : nullptr, want_xorbs ? &xorbs : nullptr)) {
         cudaStreamSynchronize(c->stream);
         return e;
     }
-    if (XetError* e = assemble_result(files, chunks, want_chunks, out_result)) return e;
+    if (XetError* e = assemble_result(files, chunks, want_chunks, out_result, &xorbs)) return e;
     prog.pu.phase = XET_PROGRESS_PHASE_FINALIZING;
     prog.pu.completed_bytes = all_bytes;
     prog.pu.completed_files = (uint32_t)n_files;
@@ -1552,8 +1654,34 @@ struct MultiPiece {
 };
 
 // Port of sharded.plan_concatenated: per device, its pieces in file order.
+// Nearest tensor boundary of a *.safetensors shard to `off`, if one lies within a quarter range and leaves both
+// neighbours room for the halo; `off` itself otherwise (other file types, unparsable headers, giant tensors).
+static uint64_t snap_to_tensor(const char* path, uint64_t size, uint64_t off, uint64_t range_bytes) {
+    const size_t len = strlen(path);
+    if (len < 12 || strcmp(path + len - 12, ".safetensors") != 0) return off;
+    XetGpuSafetensorsIndex* ix = nullptr;
+    if (XetError* e = xetgpu_safetensors_open(path, &ix)) {
+        xetgpu_free_error(e);
+        return off;
+    }
+    uint64_t best = off, best_d = range_bytes / 4 + 1;
+    for (uint64_t i = 0; i < ix->n_tensors; i++)
+        for (uint64_t m : {ix->tensors[i].begin, ix->tensors[i].end}) {
+            const uint64_t d = m > off ? m - off : off - m;
+            if (d < best_d && m >= XETGPU_RANGE_LEAD + 4096 && size - std::min(size, m) >= XETGPU_RANGE_LEAD + 4096) {
+                best_d = d;
+                best = m;
+            }
+        }
+    xetgpu_safetensors_free(ix);
+    return best;
+}
+
+// snap(f, off, range_bytes): optional policy hook that may move an in-file boundary (tensor boundaries of a shard).
+typedef std::function<uint64_t(size_t, uint64_t, uint64_t)> SnapFn;
+
 static std::vector<std::vector<MultiPiece>> plan_concatenated(const std::vector<uint64_t>& sizes, size_t world,
-                                                              uint64_t align = 4096) {
+                                                              const SnapFn& snap = nullptr, uint64_t align = 4096) {
     std::vector<uint64_t> starts(sizes.size() + 1, 0);
     for (size_t f = 0; f < sizes.size(); f++) starts[f + 1] = starts[f] + sizes[f];
     const uint64_t total = starts[sizes.size()];
@@ -1565,6 +1693,7 @@ static std::vector<std::vector<MultiPiece>> plan_concatenated(const std::vector<
         f = f ? f - 1 : 0;
         if (f >= sizes.size()) f = sizes.size() - 1;
         uint64_t off = (pos - starts[f]) / align * align;
+        if (snap && off >= min_piece && sizes[f] - off >= min_piece) off = snap(f, off, total / world);
         if (off < min_piece) off = 0;
         else if (sizes[f] - off < min_piece) off = sizes[f];
         cuts.push_back(std::max(starts[f] + off, cuts.back()));
@@ -1710,9 +1839,17 @@ extern "C" XetError* xetgpu_multi_hash_files(XetGpuMulti* m, const char* const* 
         if (XetError* e = stat_regular(paths[f], &sizes[f])) return e;
         all_bytes += sizes[f];
     }
+    if (flags & XETGPU_WANT_XORBS)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "XETGPU_WANT_XORBS is not offered by the multi-device call: a shared "
+                                                     "file's chunk list is assembled on the host; form xorbs per device");
     const bool want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
     const size_t world = (size_t)std::min<uint64_t>(m->ctx.size(), std::max<uint64_t>(1, all_bytes / m->min_bytes_per_device));
-    const auto plan = plan_concatenated(sizes, world);
+    // Boundaries inside a *.safetensors shard move to the nearest tensor boundary (safetensors.cu); a file whose
+    // header does not parse is simply cut where the equal split falls.
+    SnapFn snap = nullptr;
+    if (!(flags & XETGPU_NO_TENSOR_SNAP))
+        snap = [&](size_t f, uint64_t off, uint64_t range_bytes) -> uint64_t { return snap_to_tensor(paths[f], sizes[f], off, range_bytes); };
+    const auto plan = plan_concatenated(sizes, world, snap);
     std::vector<std::vector<size_t>> owners(n_files);   // devices that hold a piece of each file, ascending
     for (size_t d = 0; d < world; d++)
         for (const auto& p : plan[d]) owners[p.file].push_back(d);
@@ -1877,4 +2014,36 @@ extern "C" XetError* xetgpu_multi_verify_files(XetGpuMulti* m, const char* const
     XetError* e = verify_against(r, paths, expected_hex, want, n_files, out_ok);
     xetgpu_free_result(r);
     return e;
+}
+
+// Test / tooling hook: the byte ranges xetgpu_multi_hash_files would give each device for these files.
+// out_pieces receives up to cap entries of (device, file, begin, end), in device order; returns the count.
+extern "C" XetError* xetgpu_multi_plan(XetGpuMulti* m, const char* const* paths, size_t n_files, uint32_t flags,
+                                       uint64_t* out_pieces, size_t cap, size_t* out_count) {
+    if (!m || !out_count || (n_files && !paths) || (cap && !out_pieces))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_multi_plan");
+    std::vector<uint64_t> sizes(n_files);
+    uint64_t all_bytes = 0;
+    for (size_t f = 0; f < n_files; f++) {
+        if (XetError* e = stat_regular(paths[f], &sizes[f])) return e;
+        all_bytes += sizes[f];
+    }
+    const size_t world = (size_t)std::min<uint64_t>(m->ctx.size(), std::max<uint64_t>(1, all_bytes / m->min_bytes_per_device));
+    SnapFn snap = nullptr;
+    if (!(flags & XETGPU_NO_TENSOR_SNAP))
+        snap = [&](size_t f, uint64_t off, uint64_t range_bytes) -> uint64_t { return snap_to_tensor(paths[f], sizes[f], off, range_bytes); };
+    const auto plan = plan_concatenated(sizes, world, snap);
+    size_t n = 0;
+    for (size_t d = 0; d < plan.size(); d++)
+        for (const auto& p : plan[d]) {
+            if (n < cap) {
+                out_pieces[4 * n] = d;
+                out_pieces[4 * n + 1] = p.file;
+                out_pieces[4 * n + 2] = p.begin;
+                out_pieces[4 * n + 3] = p.end;
+            }
+            n++;
+        }
+    *out_count = n;
+    return nullptr;
 }

@@ -437,4 +437,97 @@ int launch_merkle(const PipelineBuffers& b, cudaStream_t st) {
     return n + 1;
 }
 
+// ---- xorb formation -------------------------------------------------------------
+// xet-core's upload side packs a file's chunks, in order, into xorbs of at most 64 MiB of chunk bytes and at most
+// 8192 chunks; a xorb's hash is merklehash::xorb_hash = aggregated_node_hash over its (chunk hash, length) list —
+// the very function K4 computes per file.  So: one thread per file walks the greedy packing over the dense chunk
+// ends (a binary search per xorb, ~N / 64 MiB steps), then the K4 finish kernel runs with "file" = xorb (every
+// xorb holds <= 8192 nodes, which is what one finish CTA handles).  The grouping policy is parity-unpinned: the
+// reference binary (hf_xet.hash_files) does not expose xorbs; the tests compare with an independent CPU twin.
+__global__ void xorb_group_kernel(uint32_t n_files, const uint64_t* __restrict__ file_chunk_base,
+                                  const uint32_t* __restrict__ file_count, const uint64_t* __restrict__ out_end,
+                                  const uint64_t* __restrict__ xorb_slot_off, uint32_t* __restrict__ xorb_count,
+                                  uint64_t* __restrict__ xorb_node_off, uint32_t* __restrict__ xorb_n,
+                                  uint64_t* __restrict__ xorb_bytes) {
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= n_files) return;
+    const uint64_t base = file_chunk_base[f];
+    const uint32_t n = file_count[f];
+    const uint64_t s0 = xorb_slot_off[f], cap = xorb_slot_off[f + 1] - s0;
+    const uint64_t* ends = out_end + base;   // file-relative exclusive ends
+    uint32_t i = 0;
+    uint64_t x = 0;
+    while (i < n) {
+        const uint64_t start = i ? ends[i - 1] : 0;
+        // largest j in (i, min(n, i + kMaxXorbChunks)] with ends[j-1] - start <= kMaxXorbBytes; j = i + 1 always fits
+        uint32_t lo = i + 1, hi = n - i > kMaxXorbChunks ? i + kMaxXorbChunks : n;
+        while (lo < hi) {
+            const uint32_t mid = lo + (hi - lo + 1) / 2;
+            if (ends[mid - 1] - start <= kMaxXorbBytes) lo = mid;
+            else hi = mid - 1;
+        }
+        if (x < cap) {
+            xorb_node_off[s0 + x] = base + i;
+            xorb_n[s0 + x] = lo - i;
+            xorb_bytes[s0 + x] = ends[lo - 1] - start;
+        }
+        x++;
+        i = lo;
+    }
+    xorb_count[f] = (uint32_t)(x < cap ? x : cap);
+    for (uint64_t k = x; k < cap; k++) {  // unused slots: empty "files" for the merkle pass
+        xorb_node_off[s0 + k] = 0;
+        xorb_n[s0 + k] = 0;
+        xorb_bytes[s0 + k] = 0;
+    }
+}
+
+// Level 0 of the xorb trees: dense chunk hashes and lengths (file-relative ends -> lengths).
+__global__ void xorb_prepare_kernel(uint32_t n_files, const uint64_t* __restrict__ scalars,
+                                    const uint64_t* __restrict__ file_chunk_base, const uint64_t* __restrict__ out_end,
+                                    const uint8_t* __restrict__ out_hash, uint8_t* __restrict__ node_hash,
+                                    uint64_t* __restrict__ node_size) {
+    const uint64_t d = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= scalars[kScalarChunks]) return;
+    uint32_t lo = 0, hi = n_files;  // last f with file_chunk_base[f] <= d
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (file_chunk_base[mid] <= d) lo = mid;
+        else hi = mid;
+    }
+    // (files without chunks share their base with the next file: the search lands on the LAST of them, which is
+    //  the one that owns d or an empty one before it — either way d > base means a predecessor in the same file)
+    while (lo + 1 < n_files && file_chunk_base[lo + 1] <= d) lo++;
+    node_size[d] = out_end[d] - (d == file_chunk_base[lo] ? 0 : out_end[d - 1]);
+    const uint4* src = reinterpret_cast<const uint4*>(out_hash + d * 32);
+    uint4* dst = reinterpret_cast<uint4*>(node_hash + d * 32);
+    dst[0] = src[0];
+    dst[1] = src[1];
+}
+
+int launch_xorbs(const PipelineBuffers& b, cudaStream_t st) {
+    if (b.n_files == 0 || b.n_xorb_slots == 0) return 0;
+    xorb_group_kernel<<<(b.n_files + 127) / 128, 128, 0, st>>>(b.n_files, b.file_chunk_base, b.file_count, b.out_end,
+                                                               b.xorb_slot_off, b.xorb_count, b.xorb_node_off, b.xorb_n,
+                                                               b.xorb_bytes);
+    int n = 1;
+    if (b.n_slots) {
+        xorb_prepare_kernel<<<(unsigned)((b.n_slots + 255) / 256), 256, 0, st>>>(
+            b.n_files, b.scalars, b.file_chunk_base, b.out_end, b.out_hash, b.node_hash[0], b.node_size[0]);
+        n++;
+    }
+    // the K4 machinery with "file" = xorb slot: node ranges start at xorb_node_off, every tree fits one finish CTA
+    PipelineBuffers m = b;
+    m.n_files = (uint32_t)b.n_xorb_slots;
+    m.slot_off = b.xorb_node_off;
+    m.file_count = b.xorb_n;
+    m.level_count[0] = b.xorb_level[0];
+    m.level_count[1] = b.xorb_level[1];
+    m.file_root = b.xorb_root;
+    m.file_hash = b.xorb_scratch;
+    m.max_nodes = kMaxXorbChunks;
+    m.chunk_len = nullptr;  // level-0 sizes are already in node_size[0]
+    return n + launch_merkle(m, st);
+}
+
 }  // namespace xetgpu

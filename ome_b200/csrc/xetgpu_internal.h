@@ -95,6 +95,16 @@ struct PipelineBuffers {
     // dense outputs
     uint64_t* out_end;          // [n_slots] file-relative ends, dense by file_chunk_base
     uint8_t* out_hash;          // [n_slots * 32]
+    // optional xorb formation (merkle.cu, launch_xorbs): file f owns xorb slots [xorb_slot_off[f], xorb_slot_off[f+1])
+    const uint64_t* xorb_slot_off;  // device [n_files+1], host-computed prefix of per-file upper bounds
+    uint64_t n_xorb_slots;
+    uint32_t* xorb_count;       // [n_files] xorbs per file
+    uint64_t* xorb_node_off;    // [n_xorb_slots+1] dense index (out_end / out_hash) of the xorb's first chunk
+    uint32_t* xorb_n;           // [n_xorb_slots] chunks in the xorb (0 = unused slot)
+    uint64_t* xorb_bytes;       // [n_xorb_slots]
+    uint8_t* xorb_root;         // [n_xorb_slots * 32] xorb_hash = aggregated_node_hash of the xorb's chunks
+    uint8_t* xorb_scratch;      // [n_xorb_slots * 32]
+    uint32_t* xorb_level[2];    // [n_xorb_slots+1] ping-pong level counts
     // scan scratch
     uint64_t* scan_partial;     // [scan_blocks_cap]
     uint64_t* scalars;          // [8] device scalars: 0 = n_cand, 1 = n_groups, 2 = n_chunks
@@ -120,6 +130,11 @@ int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_
 int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st);
 int launch_merkle(const PipelineBuffers& b, cudaStream_t st);
 int launch_gather(const PipelineBuffers& b, cudaStream_t st);
+// Xorb formation over the dense per-file chunk lists (after launch_gather and launch_merkle): greedy packing into
+// xorbs of <= kMaxXorbBytes and <= kMaxXorbChunks, one merkle root per xorb.
+int launch_xorbs(const PipelineBuffers& b, cudaStream_t st);
+constexpr uint64_t kMaxXorbBytes = 64ull << 20;
+constexpr uint32_t kMaxXorbChunks = 8192;
 int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* partial, uint64_t* total_out,
                     cudaStream_t st);
 

@@ -17,6 +17,7 @@ from . import _lib as L
 
 MEM_AUTO, MEM_HOST, MEM_DEVICE = 0, 1, 2
 WANT_CHUNKS = 1
+WANT_XORBS = 2
 CTX_STAGE_TIMING = 1
 CTX_NO_OVERLAP = 2
 
@@ -104,11 +105,16 @@ class FileList:
         return f"FileList({len(self)} files)"
 
 
+_XORB_DTYPE = np.dtype([("hash", "u1", 32), ("file", "<u8"), ("first_chunk", "<u8"), ("n_chunks", "<u8"), ("bytes", "<u8")])
+assert _XORB_DTYPE.itemsize == C.sizeof(L.XetGpuXorb)
+
+
 @dataclass
 class ChunkList:
     files: FileList                  # sequence of FileHash
     chunk_ends: Optional[np.ndarray]    # uint64 [n_chunks], file-relative exclusive ends
     chunk_hashes: Optional[np.ndarray]  # uint8 [n_chunks, 32]
+    xorbs: Optional[np.ndarray] = None  # structured [n_xorbs]: hash, file, first_chunk (within the file), n_chunks, bytes
 
     def chunks_of(self, f: int):
         fr = self.files[f]
@@ -230,11 +236,15 @@ class XetHasher:
             else:
                 ends = np.zeros(0, dtype=np.uint64)
                 hashes = np.zeros((0, 32), dtype=np.uint8)
+        xorbs = None
+        if r.n_xorbs:
+            xorbs = np.frombuffer(C.string_at(r.xorbs, r.n_xorbs * _XORB_DTYPE.itemsize), dtype=_XORB_DTYPE)
         self._lib.xetgpu_free_result(resp)
-        return ChunkList(files, ends, hashes)
+        return ChunkList(files, ends, hashes, xorbs)
 
     # -- hashing
-    def hash_buffers(self, data, offsets: Sequence[int], memory: int = MEM_AUTO, want_chunks: bool = False) -> ChunkList:
+    def hash_buffers(self, data, offsets: Sequence[int], memory: int = MEM_AUTO, want_chunks: bool = False,
+                     want_xorbs: bool = False) -> ChunkList:
         """Files packed back to back in `data` (bytes, numpy, torch tensor or raw address)."""
         addr, _, keep = _ptr_of(data)
         self._order_after_torch(data)
@@ -242,23 +252,25 @@ class XetHasher:
         n_files = max(off.size - 1, 0)
         resp = C.POINTER(L.XetGpuResult)()
         _check(self._lib.xetgpu_hash_buffers(self._ctx, addr, off.ctypes.data_as(C.POINTER(C.c_uint64)), n_files,
-                                             memory, WANT_CHUNKS if want_chunks else 0, C.byref(resp)))
+                                             memory, (WANT_CHUNKS if want_chunks else 0) | (WANT_XORBS if want_xorbs else 0),
+                                             C.byref(resp)))
         del keep
         return self._take(resp, want_chunks)
 
-    def hash_bytes(self, data, memory: int = MEM_AUTO, want_chunks: bool = False) -> ChunkList:
+    def hash_bytes(self, data, memory: int = MEM_AUTO, want_chunks: bool = False, want_xorbs: bool = False) -> ChunkList:
         _, n, _ = _ptr_of(data)
-        return self.hash_buffers(data, [0, n], memory, want_chunks)
+        return self.hash_buffers(data, [0, n], memory, want_chunks, want_xorbs)
 
     def hash_files(self, paths: Sequence[str], want_chunks: bool = False,
-                   should_cancel: Optional[Callable[[], bool]] = None) -> ChunkList:
+                   should_cancel: Optional[Callable[[], bool]] = None, want_xorbs: bool = False) -> ChunkList:
         arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
         tok = None
         if should_cancel is not None:
             cb = L.CancellationCallback(lambda _u: bool(should_cancel()))
             tok = L.XetCancellationToken(cb, None)
         resp = C.POINTER(L.XetGpuResult)()
-        _check(self._lib.xetgpu_hash_files(self._ctx, arr, len(paths), WANT_CHUNKS if want_chunks else 0,
+        _check(self._lib.xetgpu_hash_files(self._ctx, arr, len(paths),
+                                           (WANT_CHUNKS if want_chunks else 0) | (WANT_XORBS if want_xorbs else 0),
                                            C.byref(tok) if tok is not None else None, C.byref(resp)))
         return self._take(resp, want_chunks)
 
@@ -413,6 +425,15 @@ class XetMultiHasher:
         _check(self._lib.xetgpu_multi_hash_files(self._ctx, arr, len(paths), WANT_CHUNKS if want_chunks else 0,
                                                  C.byref(tok) if tok is not None else None, C.byref(resp)))
         return XetHasher._take(self, resp, want_chunks)
+
+    def plan(self, paths: Sequence[str], tensor_snap: bool = True) -> list:
+        """[(device index, file index, begin, end)] — the byte ranges hash_files gives each device."""
+        arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+        cap = 2 * len(paths) + 4 * self.n_devices + 4
+        out = (C.c_uint64 * (4 * cap))()
+        n = C.c_size_t()
+        _check(self._lib.xetgpu_multi_plan(self._ctx, arr, len(paths), 0 if tensor_snap else 4, out, cap, C.byref(n)))
+        return [tuple(int(out[4 * i + k]) for k in range(4)) for i in range(min(n.value, cap))]
 
     def verify_files(self, paths: Sequence[str], expected_hex: Sequence[Optional[str]]) -> list:
         n = len(paths)

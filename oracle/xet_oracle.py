@@ -54,6 +54,8 @@ def lib() -> ctypes.CDLL:
         L.xo_hex.argtypes = [_u8p, ctypes.c_char_p]
         L.xo_from_hex.argtypes = [ctypes.c_char_p, _u8p]
         L.xo_from_hex.restype = ctypes.c_int
+        L.xo_xorbs.argtypes = [_u8p, _u64p, ctypes.c_size_t, _u64p, _u8p, ctypes.c_size_t]
+        L.xo_xorbs.restype = ctypes.c_size_t
         L.xo_splitmix_fill.argtypes = [ctypes.c_uint64, ctypes.c_uint64, _u8p, ctypes.c_uint64]
         _lib = L
     return _lib
@@ -128,6 +130,19 @@ def file_hash_from_chunks(hashes: np.ndarray, sizes: np.ndarray) -> bytes:
     out = np.zeros(32, dtype=np.uint8)
     lib().xo_file_hash(_p8(h), _p64(s), s.size, _p8(out))
     return out.tobytes()
+
+
+def xorbs(hashes: np.ndarray, sizes: np.ndarray):
+    """Greedy xorb formation over one file's chunk list (<= 64 MiB and <= 8192 chunks per xorb; grouping parity
+    unpinned, see xo_xorbs).  Returns (starts uint64 [n_xorbs + 1], xorb hashes uint8 [n_xorbs, 32])."""
+    h = np.ascontiguousarray(hashes, dtype=np.uint8).reshape(-1, 32)
+    s = np.ascontiguousarray(sizes, dtype=np.uint64)
+    n = s.size
+    cap = n + 1
+    starts = np.zeros(cap + 1, dtype=np.uint64)
+    roots = np.zeros((cap, 32), dtype=np.uint8)
+    c = lib().xo_xorbs(_p8(h), _p64(s), n, _p64(starts), _p8(roots), cap)
+    return starts[:c + 1].copy(), roots[:c].copy()
 
 
 @dataclass

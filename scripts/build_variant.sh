@@ -9,7 +9,7 @@ mkdir -p $out
 NVCC=/usr/local/cuda/bin/nvcc
 FLAGS="-O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr"
 objs=""
-for f in gear resolve chunk_hash merkle merkle_static api; do
+for f in gear resolve chunk_hash merkle merkle_static safetensors api; do
   $NVCC $FLAGS "$@" -c ome_b200/csrc/$f.cu -o $out/$f.o 2> $out/$f.log &
   objs="$objs $out/$f.o"
 done

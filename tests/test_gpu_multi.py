@@ -137,3 +137,33 @@ def test_reentrant_call_from_progress_handler_is_refused(hasher, tmp_path):
     _check(cl, datas)
     assert got["err"] is not None and got["err"].code == 1 and "re-entrant" in got["err"].message
     assert "total_ms" in got["timings"]
+
+
+def test_shared_safetensors_shard_is_cut_on_tensor_boundaries(tmp_path, monkeypatch):
+    """f4: a *.safetensors shard shared between workers has its in-file boundaries on tensor boundaries (plan), and
+    its hash does not depend on where they fall."""
+    import ome_b200
+    from ome_b200 import safetensors as st
+    from test_safetensors import shard
+    monkeypatch.setenv("XETGPU_MULTI_MIN_BYTES", str(1 << 20))
+    mib = 1 << 20
+    tensors = [(f"model.layers.{i}.w", "BF16", [mib // 2 * (1 + i % 3)], mib * (1 + i % 3)) for i in range(20)]
+    raw = bytearray(shard(tensors))
+    body = xet_inputs.splitmix_bytes(48, len(raw))
+    hdr_len = 8 + int.from_bytes(raw[:8], "little")
+    raw[hdr_len:] = body[hdr_len:].tobytes()             # random payload behind a real header
+    p = tmp_path / "model-00001-of-00001.safetensors"
+    p.write_bytes(bytes(raw))
+    other = tmp_path / "tokenizer.json"
+    other.write_bytes(b"{}")
+    ix = st.open_index(str(p))
+    marks = {t.begin for t in ix.tensors} | {t.end for t in ix.tensors}
+    data = np.frombuffer(bytes(raw), dtype=np.uint8)
+    with ome_b200.XetMultiHasher([0, 0, 0]) as m:
+        plan = m.plan([str(p), str(other)])
+        cuts = sorted({b for _, f, b, e in plan if f == 0 and b > 0})
+        assert len(cuts) == 2 and all(c in marks for c in cuts), (cuts, sorted(marks)[:5])
+        raw_cuts = sorted({b for _, f, b, e in m.plan([str(p), str(other)], tensor_snap=False) if f == 0 and b > 0})
+        assert raw_cuts != cuts and all(c % 4096 == 0 for c in raw_cuts)
+        cl = m.hash_files([str(p), str(other)], want_chunks=True)
+    _check(cl, [data, np.frombuffer(b"{}", dtype=np.uint8)])

@@ -458,3 +458,57 @@ def test_reference_fixture_files_on_gpu(hasher):
     assert cl.files[0].size == exp[base + "model-1-of-2.safetensors"]["n"]
     for f, p in enumerate(paths):
         check_against_oracle(cl, f, np.fromfile(p, dtype=np.uint8))
+
+
+def _oracle_xorbs(data):
+    ref = xet_oracle.hash_file(data)
+    sizes = np.diff(np.concatenate([[0], ref.chunk_ends]).astype(np.uint64)).astype(np.uint64)
+    starts, roots = xet_oracle.xorbs(ref.chunk_hashes, sizes)
+    return ref, sizes, starts, roots
+
+
+def _check_xorbs(cl, datas):
+    """XETGPU_WANT_XORBS output vs the oracle twin (oracle/xet_oracle.c xo_xorbs).  Grouping policy parity is
+    unpinned (hf_xet does not expose xorbs); the xorb hash function is the pinned aggregated_node_hash."""
+    x = cl.xorbs
+    pos = 0
+    for f, d in enumerate(datas):
+        ref, sizes, starts, roots = _oracle_xorbs(d)
+        n = roots.shape[0]
+        mine = x[pos:pos + n] if n else x[:0]
+        assert n == 0 or (mine["file"] == f).all(), f
+        assert [int(v) for v in mine["first_chunk"]] == [int(v) for v in starts[:-1]], f
+        assert [int(v) for v in mine["n_chunks"]] == [int(starts[i + 1] - starts[i]) for i in range(n)], f
+        assert [int(v) for v in mine["bytes"]] == [int(sizes[int(starts[i]):int(starts[i + 1])].sum()) for i in range(n)], f
+        assert np.array_equal(mine["hash"], roots), f
+        assert all(int(b) <= (64 << 20) and int(c) <= 8192 for b, c in zip(mine["bytes"], mine["n_chunks"]))
+        pos += n
+    assert pos == (0 if x is None else x.shape[0])
+
+
+def test_xorb_formation_matches_oracle(hasher, tmp_path):
+    specs = [[["splitmix", 61, (150 << 20) + 3]],            # three xorbs, the byte limit binds
+             [],                                              # empty file: no xorb
+             [["splitmix", 62, 70001]],                       # one xorb
+             [["repeat", xet_inputs.W_HEX, (80 << 20) // 64]],  # candidates everywhere: 8192-byte chunks, both limits bind
+             [["ascii", "x"]]]                                # single one-byte chunk: xorb hash == chunk hash
+    datas = [xet_inputs.build(s) for s in specs]
+    off = np.concatenate([[0], np.cumsum([d.size for d in datas])]).astype(np.uint64)
+    cl = hasher.hash_buffers(np.concatenate(datas), off, want_chunks=True, want_xorbs=True)
+    for f, d in enumerate(datas):
+        check_against_oracle(cl, f, d)
+    _check_xorbs(cl, datas)
+    assert cl.xorbs.shape[0] >= 6
+    # the same through the file entry point, without the chunk lists
+    paths = []
+    for i, d in enumerate(datas):
+        p = tmp_path / f"x{i}.bin"
+        d.tofile(p)
+        paths.append(str(p))
+    small = __import__("ome_b200").XetHasher(max_batch_bytes=100 << 20)   # several batches: file indices are remapped
+    try:
+        cl2 = small.hash_files(paths, want_xorbs=True)
+    finally:
+        small.close()
+    _check_xorbs(cl2, datas)
+    assert hasher.hash_files(paths).xorbs is None

@@ -39,7 +39,7 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: xetsum [--chunks] FILE... | xetsum -c LISTFILE\n");
         return 2;
     }
-    xetgpu_version_0_1_0();
+    xetgpu_version_0_2_0();
     XetGpuContext* ctx = nullptr;
     XetGpuConfig cfg = {};
     cfg.device = -1;
