@@ -19,6 +19,8 @@
 // Message words are read with LDS.32 from the row (row stride 528 B = 132 words: lanes l, l+8,
 // l+16, l+24 share a bank — a 4-way conflict that costs ~68 of the ~1000 issue cycles of a
 // compression) and realigned with one funnel shift per word for the chunk's byte offset.
+#include <algorithm>
+
 #include "blake3_dev.cuh"
 #include "tma.cuh"
 #include "xetgpu_internal.h"
@@ -180,34 +182,98 @@ __global__ void __launch_bounds__(kLeafThreads)
     dst[1] = make_uint4(a[4], a[5], a[6], a[7]);
 }
 
-// K3b: fold a chunk's group values (complete 4-leaf subtrees, the last possibly partial) into the
-// chunk hash.  Pairing neighbours level by level and promoting an odd tail unchanged reproduces
-// BLAKE3's left-heavy tree.  One thread per chunk; <= 31 compressions.
-__global__ void chunk_tree_kernel(uint64_t n_slots, const uint32_t* __restrict__ slot_groups,
-                                  const uint64_t* __restrict__ group_off, uint32_t* __restrict__ group_cv,
-                                  uint8_t* __restrict__ chunk_hash) {
-    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
-    const uint32_t ng = slot_groups[s];
-    if (ng <= 1) return;  // single-group chunks were finalised by the leaf kernel
+// K3b: fold a chunk's group values (complete 4-leaf subtrees, the last possibly partial) into the chunk hash.
+// Pairing neighbours level by level and promoting an odd tail unchanged reproduces BLAKE3's left-heavy tree.
+// A chunk holds at most 32 groups (128 KiB / 4 KiB).  Eight lanes share a chunk: a lane loads four consecutive
+// group values (128 contiguous bytes) and folds them in registers (two levels), then three more levels run across
+// the eight lanes with warp shuffles — five dependent compressions per chunk instead of up to 31, and four chunks
+// per warp, so even a 1 GiB file (16 k chunks) fills the SMs.
+constexpr int kTreeLanes = 8;           // lanes per chunk
+constexpr int kTreeThreads = 128;
+
+__device__ __noinline__ void tree_parent(uint32_t (&l)[8], const uint32_t (&r)[8], bool root) {
     const uint32_t key[8] = XG_DATA_KEY_WORDS;
-    uint4* cvs = reinterpret_cast<uint4*>(group_cv + group_off[s] * 8);
-    for (uint32_t stride = 1; stride < ng; stride <<= 1) {
-        const bool last = stride * 2 >= ng;
-        for (uint32_t i = 0; i + stride < ng; i += 2 * stride) {
-            uint4 l0 = cvs[2 * i], l1 = cvs[2 * i + 1];
-            uint4 r0 = cvs[2 * (i + stride)], r1 = cvs[2 * (i + stride) + 1];
-            uint32_t l[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
-            uint32_t r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-            uint32_t o[8];
-            b3_parent(key, l, r, last, o);
-            cvs[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
-            cvs[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+    uint32_t o[8];
+    b3_parent(key, l, r, root, o);
+#pragma unroll
+    for (int i = 0; i < 8; i++) l[i] = o[i];
+}
+
+__device__ __forceinline__ void chunk_tree_item(uint64_t d, uint64_t n_chunks, uint32_t lane, uint32_t sub, uint32_t n_files,
+                                                const uint64_t* __restrict__ file_chunk_base,
+                                                const uint64_t* __restrict__ slot_off, const uint32_t* __restrict__ slot_groups,
+                                                const uint64_t* __restrict__ group_off, const uint32_t* __restrict__ group_cv,
+                                                uint8_t* __restrict__ chunk_hash) {
+    uint64_t s = 0;
+    uint32_t ng = 0;
+    if (d < n_chunks) {
+        uint32_t lo = 0, hi = n_files;   // last f with file_chunk_base[f] <= d (owner of chunk d)
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (file_chunk_base[mid] <= d) lo = mid;
+            else hi = mid;
+        }
+        s = slot_off[lo] + (d - file_chunk_base[lo]);
+        ng = slot_groups[s];             // <= 1: finalised by the leaf kernel
+    }
+    const bool live = ng > 1;
+    if (!__any_sync(0xffffffffu, live)) return;
+    // this lane's items: groups [4 sub, 4 sub + cnt)
+    const uint32_t cnt = live && 4u * sub < ng ? min(4u, ng - 4u * sub) : 0u;
+    uint32_t a0[8], a1[8], a2[8], a3[8];
+    const uint4* src = reinterpret_cast<const uint4*>(group_cv + (live ? (group_off[s] + 4u * sub) * 8 : 0));
+#define XG_LOAD(dst, k)                                                     \
+    if (cnt > (k)) {                                                        \
+        const uint4 x = src[2 * (k)], y = src[2 * (k) + 1];                 \
+        dst[0] = x.x; dst[1] = x.y; dst[2] = x.z; dst[3] = x.w;             \
+        dst[4] = y.x; dst[5] = y.y; dst[6] = y.z; dst[7] = y.w;             \
+    }
+    XG_LOAD(a0, 0) XG_LOAD(a1, 1) XG_LOAD(a2, 2) XG_LOAD(a3, 3)
+#undef XG_LOAD
+    // level 1 (inside the lane): (a0,a1) and (a2,a3); the merge is the root one iff it leaves a single item
+    if (__any_sync(0xffffffffu, cnt >= 2)) {
+        if (cnt >= 2) tree_parent(a0, a1, ng == 2);
+    }
+    if (__any_sync(0xffffffffu, cnt == 4)) {
+        if (cnt == 4) tree_parent(a2, a3, false);
+    }
+    // level 2: (a0', a2') — a2 is promoted unchanged when the lane holds three items
+    if (__any_sync(0xffffffffu, cnt >= 3)) {
+        if (cnt >= 3) tree_parent(a0, a2, ng <= 4);
+    }
+    // levels 3..5 across the lanes of the chunk: lane i takes lane i + d when that lane holds a value
+    const uint32_t nl = (ng + 3u) / 4u;   // lanes of this chunk that hold a value (0 if not live)
+#pragma unroll 1
+    for (uint32_t d = 1; d < kTreeLanes; d <<= 1) {
+        uint32_t r[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) r[i] = __shfl_down_sync(0xffffffffu, a0[i], d, kTreeLanes);
+        const bool merge = live && (sub & (2 * d - 1)) == 0 && sub + d < nl;
+        if (__any_sync(0xffffffffu, merge)) {
+            if (merge) tree_parent(a0, r, nl <= 2 * d);
         }
     }
-    uint4* dst = reinterpret_cast<uint4*>(chunk_hash + s * 32);
-    dst[0] = cvs[0];
-    dst[1] = cvs[1];
+    if (live && sub == 0) {
+        uint4* dst = reinterpret_cast<uint4*>(chunk_hash + s * 32);
+        dst[0] = make_uint4(a0[0], a0[1], a0[2], a0[3]);
+        dst[1] = make_uint4(a0[4], a0[5], a0[6], a0[7]);
+    }
+}
+
+// Chunks are addressed densely (d-th chunk of the batch, through the scan of the per-file chunk counts): chunk SLOTS
+// are per-file upper bounds, about eight times the real count on ordinary data, and the grid is sized on the host.
+__global__ void __launch_bounds__(kTreeThreads)
+    chunk_tree_kernel(const uint64_t* __restrict__ scalars, uint32_t n_files, const uint64_t* __restrict__ file_chunk_base,
+                      const uint64_t* __restrict__ slot_off, const uint32_t* __restrict__ slot_groups,
+                      const uint64_t* __restrict__ group_off, const uint32_t* __restrict__ group_cv,
+                      uint8_t* __restrict__ chunk_hash) {
+    const uint32_t lane = threadIdx.x & 31u, sub = lane & (kTreeLanes - 1);
+    const uint64_t n_chunks = scalars[kScalarChunks];
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x / kTreeLanes;
+    // (the loop bound is rounded up to a whole warp's worth of chunks so that all 32 lanes stay together)
+    for (uint64_t d0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x - lane) / kTreeLanes; d0 < n_chunks; d0 += stride)
+        chunk_tree_item(d0 + lane / kTreeLanes, n_chunks, lane, sub, n_files, file_chunk_base, slot_off, slot_groups, group_off,
+                        group_cv, chunk_hash);
 }
 
 void init_chunk_hash_kernels() {
@@ -223,8 +289,13 @@ int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st) {
     leaf_group_kernel<<<blocks, kLeafThreads, kLeafSmem, st>>>(b.data, b.scalars, b.group_chunk, b.group_off,
                                                                b.chunk_start, b.chunk_len, b.group_cv, b.chunk_hash);
     if (b.ev_kernel[3]) cudaEventRecord(b.ev_kernel[3], st);
-    chunk_tree_kernel<<<(unsigned)((b.n_slots + 127) / 128), 128, 0, st>>>(b.n_slots, b.slot_groups, b.group_off,
-                                                                          b.group_cv, b.chunk_hash);
+    // dense chunk numbering: exclusive scan of the per-file chunk counts (+ the batch's chunk count), also used by
+    // the gather and by the xorb pass
+    n += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial, b.scalars + kScalarChunks, st);
+    const uint64_t want = (b.n_slots * kTreeLanes + kTreeThreads - 1) / kTreeThreads;
+    const unsigned tblocks = (unsigned)std::min<uint64_t>(want, (uint64_t)b.sm_count * 16);
+    chunk_tree_kernel<<<tblocks ? tblocks : 1, kTreeThreads, 0, st>>>(b.scalars, b.n_files, b.file_chunk_base, b.slot_off,
+                                                                      b.slot_groups, b.group_off, b.group_cv, b.chunk_hash);
     return n + 2;
 }
 

@@ -12,6 +12,8 @@
 #include <cuda.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "tma.cuh"
 #include "xetgpu_internal.h"
 #include "../../include/xet_gear_table.h"
@@ -422,7 +424,7 @@ __global__ void __launch_bounds__(1024) scan_small_kernel(const uint32_t* __rest
 
 int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* partial, uint64_t* total_out,
                     cudaStream_t st) {
-    if (n <= 16384) {
+    if (n <= 2048) {  // measured: one CTA takes 42 us for 16 k entries, the three-kernel form 12 us
         scan_small_kernel<<<1, 1024, 0, st>>>(in, n, out, total_out);
         return 1;
     }
@@ -432,6 +434,34 @@ int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* par
     scan_partials_kernel<<<1, 1024, 0, st>>>(partial, nblocks, total_out);
     scan_apply_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(in, n, partial, out);
     return 3;
+}
+
+// ------------------------------------------------------------------------- cooperative-launch gate
+namespace {
+struct CoopGate {
+    std::mutex mu;
+    cudaEvent_t done = nullptr;
+};
+CoopGate g_coop_gate[64];
+}  // namespace
+
+cudaError_t launch_cooperative_gated(const void* kernel, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t st) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    CoopGate& g = g_coop_gate[dev];
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.done) {
+        e = cudaEventCreateWithFlags(&g.done, cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+    } else {
+        e = cudaStreamWaitEvent(st, g.done, 0);
+        if (e != cudaSuccess) return e;
+    }
+    e = cudaLaunchCooperativeKernel(kernel, grid, block, args, smem, st);
+    if (e != cudaSuccess) return e;
+    return cudaEventRecord(g.done, st);
 }
 
 // ------------------------------------------------------------------------------------ launcher

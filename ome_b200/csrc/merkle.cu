@@ -12,6 +12,10 @@
 // Every file in the batch advances one level per round of launches: the grouping kernels below,
 // then one thread per new node that formats and hashes its lines.  This stage touches 40 bytes
 // per ~64 KiB chunk, so it is launch/latency-bound, not bandwidth-bound.
+#include <stdio.h>
+
+#include <algorithm>
+
 #include "blake3_dev.cuh"
 #include "xetgpu_internal.h"
 
@@ -47,12 +51,11 @@ __device__ __forceinline__ uint32_t file_of_slot_g(const uint64_t* __restrict__ 
     return lo;
 }
 
-__global__ void merkle_block_map_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
-                                        const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
-                                        uint64_t* __restrict__ block_bits, uint64_t* __restrict__ map_out,
-                                        uint64_t* __restrict__ map_cnt) {
-    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
+// A: table of one 32-node block (slot s of its file's range).
+__device__ __forceinline__ void block_map_item(uint64_t s, const uint64_t* __restrict__ slot_off, uint32_t n_files,
+                                               const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
+                                               uint64_t* __restrict__ block_bits, uint64_t* __restrict__ map_out,
+                                               uint64_t* __restrict__ map_cnt) {
     const uint32_t f = file_of_slot_g(slot_off, n_files, s);
     const uint64_t base = slot_off[f];
     const uint32_t n = cur_count[f];
@@ -79,19 +82,16 @@ __global__ void merkle_block_map_kernel(const uint64_t* __restrict__ slot_off, u
     map_cnt[s] = mc;
 }
 
-// One WARP per file: the block tables of 32 consecutive blocks are loaded coalesced, one per lane,
-// and the chain is then advanced through them with register shuffles only (no memory latency on
-// the sequential path); every lane runs the same uniform recurrence and keeps the state at which
-// the chain entered its own block.
-__global__ void merkle_compose_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files,
-                                      const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
-                                      const uint64_t* __restrict__ map_out, const uint64_t* __restrict__ map_cnt,
-                                      uint32_t* __restrict__ block_entry, uint32_t* __restrict__ block_base,
-                                      uint32_t* __restrict__ next_count, uint32_t* __restrict__ group_start,
-                                      uint8_t* __restrict__ file_root) {
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (f >= n_files) return;
+// B: one WARP per file: the block tables of 32 consecutive blocks are loaded coalesced, one per lane, and the chain
+// is then advanced through them with register shuffles only (no memory latency on the sequential path); every lane
+// runs the same uniform recurrence and keeps the state at which the chain entered its own block.
+// Returns the file's node count at the next level (0 for a finished or empty file).
+__device__ __forceinline__ uint32_t compose_file(uint32_t f, uint32_t lane, const uint64_t* __restrict__ slot_off,
+                                                 const uint8_t* __restrict__ cur_hash, const uint32_t* __restrict__ cur_count,
+                                                 const uint64_t* __restrict__ map_out, const uint64_t* __restrict__ map_cnt,
+                                                 uint32_t* __restrict__ block_entry, uint32_t* __restrict__ block_base,
+                                                 uint32_t* __restrict__ next_count, uint32_t* __restrict__ group_start,
+                                                 uint8_t* __restrict__ file_root) {
     const uint32_t n = cur_count[f];
     const uint64_t base = slot_off[f];
     if (n <= 1) {
@@ -99,7 +99,7 @@ __global__ void merkle_compose_kernel(const uint64_t* __restrict__ slot_off, uin
             reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32)[lane] =
                 reinterpret_cast<const uint4*>(cur_hash + base * 32)[lane];
         if (lane == 0) next_count[f] = 0;
-        return;
+        return 0;
     }
     const uint32_t nb = (n + 31) / 32;
     uint32_t o = 0, total = 0;
@@ -128,14 +128,14 @@ __global__ void merkle_compose_kernel(const uint64_t* __restrict__ slot_off, uin
         group_start[base + total] = n;  // sentinel; total <= (n + 2) / 3 < n for n >= 2
         next_count[f] = total;
     }
+    return total;
 }
 
-__global__ void merkle_emit_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
-                                   const uint32_t* __restrict__ cur_count, const uint64_t* __restrict__ block_bits,
-                                   const uint32_t* __restrict__ block_entry, const uint32_t* __restrict__ block_base,
-                                   uint32_t* __restrict__ group_start) {
-    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
+// C: replay one block from its known entry offset and write the group starts.
+__device__ __forceinline__ void emit_item(uint64_t s, const uint64_t* __restrict__ slot_off, uint32_t n_files,
+                                          const uint32_t* __restrict__ cur_count, const uint64_t* __restrict__ block_bits,
+                                          const uint32_t* __restrict__ block_entry, const uint32_t* __restrict__ block_base,
+                                          uint32_t* __restrict__ group_start) {
     const uint32_t f = file_of_slot_g(slot_off, n_files, s);
     const uint64_t base = slot_off[f];
     const uint32_t n = cur_count[f];
@@ -260,181 +260,299 @@ __device__ __forceinline__ void hash_node_message(const uint32_t* msg, uint32_t 
     }
 }
 
-__global__ void merkle_hash_kernel(const uint64_t* __restrict__ slot_off, uint32_t n_files, uint64_t n_slots,
-                                   const uint8_t* __restrict__ cur_hash, const uint64_t* __restrict__ cur_size,
-                                   const uint32_t* __restrict__ next_count, const uint32_t* __restrict__ group_start,
-                                   uint8_t* __restrict__ next_hash, uint64_t* __restrict__ next_size) {
-    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
-    const uint32_t f = file_of_slot_m(slot_off, n_files, s);
-    const uint64_t base = slot_off[f];
-    const uint32_t gi = (uint32_t)(s - base);
-    if (gi >= next_count[f]) return;
-    const uint32_t c0 = group_start[base + gi], c1 = group_start[base + gi + 1];
+// D: one new node: format its children's lines and hash them.
+__device__ __forceinline__ void hash_node_item(const uint8_t* __restrict__ cur_hash, const uint64_t* __restrict__ cur_size,
+                                               uint64_t first_child, uint32_t n_children, uint8_t* __restrict__ dst_hash,
+                                               uint64_t* __restrict__ dst_size) {
     uint32_t msg[224];
     uint64_t total;
-    const uint32_t len = format_node(cur_hash, cur_size, base + c0, c1 - c0, msg, &total);
+    const uint32_t len = format_node(cur_hash, cur_size, first_child, n_children, msg, &total);
     uint32_t cv[8];
     hash_node_message(msg, len, cv);
-    uint4* dst = reinterpret_cast<uint4*>(next_hash + s * 32);
+    uint4* dst = reinterpret_cast<uint4*>(dst_hash);
     dst[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
     dst[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
-    next_size[s] = total;
+    *dst_size = total;
 }
 
-// ---- last levels in one launch ------------------------------------------------------------------
-// Once every file's level is known to hold at most kFinishNodes nodes, one CTA per file runs all
-// remaining levels by itself (same grouping tables, kept in shared memory), which removes four
-// launches per level from the latency-bound tail of the tree.
+// ---- the whole stage in ONE cooperative launch ----------------------------------------------------------
+// K4 is latency-bound (40 bytes of input per ~64 KiB chunk), so what it costs is launches and the gaps between them:
+// as separate kernels it took four launches per level plus three more, and the number of level rounds had to come
+// from a host-side upper bound (chunk slots, ~8x the real chunk count), i.e. two or three empty rounds per call.
+// Here one cooperative grid runs every phase with grid-wide barriers in between and decides ON THE DEVICE when the
+// level rounds are over:
+//   0   level-0 sizes from the chunk lengths, level counts from the per-file chunk counts
+//   repeat while some file holds more than kFinishNodes nodes:   A block tables | B compose | C emit | D hash
+//   then one CTA per file (CTAs stride over the files) finishes its tree in shared memory and hashes the root
+//   under the zero salt (file hash).
 constexpr uint32_t kFinishNodes = 8192;
-constexpr uint32_t kFinishThreads = 256;  // one 32-node block per thread
-static_assert(kFinishNodes == kFinishThreads * 32, "one block per thread");
+constexpr uint32_t kFinishBlocks = kFinishNodes / 32;   // 32-node blocks per finishing file
+constexpr int kMerkleThreads = 512;
 
-__global__ void __launch_bounds__(kFinishThreads)
-    merkle_finish_kernel(const uint64_t* __restrict__ slot_off, const uint32_t* __restrict__ level_count,
-                         uint8_t* hash_a, uint64_t* size_a, uint8_t* hash_b, uint64_t* size_b,
-                         uint8_t* __restrict__ file_root) {
-    __shared__ uint64_t s_bits[kFinishThreads], s_out[kFinishThreads], s_cnt[kFinishThreads];
-    __shared__ uint32_t s_entry[kFinishThreads], s_base[kFinishThreads];
+struct MerkleArgs {
+    const uint64_t* slot_off;
+    uint32_t n_files;
+    uint64_t n_slots;
+    const uint32_t* chunk_len;     // nullptr: level-0 sizes are already in node_size[0]
+    const uint32_t* file_count;
+    uint8_t* node_hash[2];
+    uint64_t* node_size[2];
+    uint32_t* level_count[2];
+    uint32_t* group_start;
+    uint64_t* mk_bits;
+    uint64_t* mk_out;
+    uint64_t* mk_cnt;
+    uint32_t* mk_entry;
+    uint32_t* mk_base;
+    uint8_t* file_root;
+    uint8_t* file_hash;
+    uint32_t* round_max;           // [2] device words: largest next-level count seen in a round
+};
+
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t& epoch, uint32_t n_blocks);
+
+__global__ void __launch_bounds__(kMerkleThreads) merkle_coop_kernel(MerkleArgs a, uint32_t* barrier_word) {
+    __shared__ uint64_t s_bits[kFinishBlocks], s_out[kFinishBlocks], s_cnt[kFinishBlocks];
+    __shared__ uint32_t s_entry[kFinishBlocks], s_base[kFinishBlocks];
     __shared__ uint32_t s_start[kFinishNodes / 3 + 4];
     __shared__ uint32_t s_ng;
-    const uint32_t f = blockIdx.x, tid = threadIdx.x;
-    uint32_t n = level_count[f];
-    if (n == 0 || n > kFinishNodes) return;  // empty / already latched / (never: host bound) too large
-    const uint64_t base = slot_off[f];
-    uint8_t* cur_hash = hash_a + base * 32;
-    uint64_t* cur_size = size_a + base;
-    uint8_t* nxt_hash = hash_b + base * 32;
-    uint64_t* nxt_size = size_b + base;
-    while (n > 1) {
-        const uint32_t nb = (n + 31) / 32;
-        if (tid < nb) {  // A: block table
-            const uint32_t first = tid * 32;
-            uint64_t bits = 0;
-            for (uint32_t i = 0; i < 40 && first + i < n; i++)
-                bits |= (uint64_t)((cur_hash[(uint64_t)(first + i) * 32 + 24] & 3u) == 0u) << i;
-            uint64_t mo = 0, mc = 0;
-            for (uint32_t o = 0; o < 9; o++) {
-                uint32_t r = o, cnt = 0;
-                while (r < 32 && first + r < n) {
-                    r += group_len(bits, r, n - (first + r));
-                    cnt++;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint64_t gtid = (uint64_t)blockIdx.x * blockDim.x + tid;
+    const uint64_t gthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint32_t gwarp = (uint32_t)(gtid >> 5), gwarps = (uint32_t)(gthreads >> 5);
+    uint32_t epoch = 0;
+#ifdef XG_MERKLE_TRACE
+    unsigned long long tr[40];
+    int ntr = 0;
+#define XG_TR() do { if (gtid == 0 && ntr < 40) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tr[ntr++] = t_; } } while (0)
+#else
+#define XG_TR() do {} while (0)
+#endif
+    XG_TR();
+
+    // Slot loops hand consecutive groups of 32 slots to consecutive CTAs: the live slots of a level are the first
+    // few of every file's range, and a plain grid-stride loop would give all of them to a handful of CTAs.
+    const uint32_t wpb = blockDim.x >> 5, lw = tid >> 5;
+#define XG_FOR_SLOTS(s)                                                                                          \
+    for (uint64_t _sw = (uint64_t)lw * gridDim.x + blockIdx.x, s = _sw * 32 + lane; _sw * 32 < a.n_slots;        \
+         _sw += (uint64_t)wpb * gridDim.x, s = _sw * 32 + lane)                                                  \
+        if (s < a.n_slots)
+
+    // phase 0
+    if (a.chunk_len)
+        for (uint64_t s = gtid; s < a.n_slots; s += gthreads) a.node_size[0][s] = a.chunk_len[s];
+    uint32_t local_max = 0;
+    for (uint64_t f = gtid; f < a.n_files; f += gthreads) {
+        const uint32_t c = a.file_count[f];
+        a.level_count[0][f] = c;
+        local_max = max(local_max, c);
+    }
+    if (gtid == 0) a.round_max[1] = 0;
+    if (local_max) atomicMax(&a.round_max[0], local_max);   // round_max[0] was zeroed by the host before the launch
+    grid_barrier(barrier_word, epoch, gridDim.x);
+    XG_TR();
+
+    int cur = 0;
+    uint32_t r = 0;   // round_max[r & 1] holds the largest count of the level the grid is about to process
+    while (*(volatile uint32_t*)&a.round_max[r & 1] > kFinishNodes) {
+        const uint8_t* cur_hash = a.node_hash[cur];
+        const uint64_t* cur_size = a.node_size[cur];
+        const uint32_t* cur_count = a.level_count[cur];
+        uint32_t* next_count = a.level_count[cur ^ 1];
+        XG_FOR_SLOTS(s) block_map_item(s, a.slot_off, a.n_files, cur_hash, cur_count, a.mk_bits, a.mk_out, a.mk_cnt);
+        XG_TR();
+        grid_barrier(barrier_word, epoch, gridDim.x);
+        XG_TR();
+        uint32_t mx = 0;
+        for (uint32_t f = gwarp; f < a.n_files; f += gwarps)
+            mx = max(mx, compose_file(f, lane, a.slot_off, cur_hash, cur_count, a.mk_out, a.mk_cnt, a.mk_entry, a.mk_base,
+                                      next_count, a.group_start, a.file_root));
+        if (lane == 0 && mx) atomicMax(&a.round_max[(r + 1) & 1], mx);
+        XG_TR();
+        grid_barrier(barrier_word, epoch, gridDim.x);
+        XG_TR();
+        XG_FOR_SLOTS(s) emit_item(s, a.slot_off, a.n_files, cur_count, a.mk_bits, a.mk_entry, a.mk_base, a.group_start);
+        XG_TR();
+        grid_barrier(barrier_word, epoch, gridDim.x);
+        XG_TR();
+        XG_FOR_SLOTS(s) {
+            const uint32_t f = file_of_slot_g(a.slot_off, a.n_files, s);
+            const uint64_t base = a.slot_off[f];
+            const uint32_t gi = (uint32_t)(s - base);
+            if (gi >= next_count[f]) continue;
+            const uint32_t c0 = a.group_start[base + gi], c1 = a.group_start[base + gi + 1];
+            hash_node_item(cur_hash, cur_size, base + c0, c1 - c0, a.node_hash[cur ^ 1] + s * 32, a.node_size[cur ^ 1] + s);
+        }
+        if (gtid == 0) a.round_max[r & 1] = 0;   // read by everyone before the barrier after phase A; free for round r + 2
+        XG_TR();
+        grid_barrier(barrier_word, epoch, gridDim.x);
+        XG_TR();
+        cur ^= 1;
+        r++;
+    }
+
+#undef XG_FOR_SLOTS
+    // finish: one CTA per file, all remaining levels in shared memory
+    for (uint32_t f = blockIdx.x; f < a.n_files; f += gridDim.x) {
+        uint32_t n = a.level_count[cur][f];
+        const uint64_t base = a.slot_off[f];
+        uint8_t* cur_hash = a.node_hash[cur] + base * 32;
+        uint64_t* cur_size = a.node_size[cur] + base;
+        uint8_t* nxt_hash = a.node_hash[cur ^ 1] + base * 32;
+        uint64_t* nxt_size = a.node_size[cur ^ 1] + base;
+        const bool run = n >= 1 && n <= kFinishNodes;   // 0: empty file, or root latched during the level rounds
+        while (run && n > 1) {
+            const uint32_t nb = (n + 31) / 32;
+            if (tid < nb) {  // A: block table
+                const uint32_t first = tid * 32;
+                uint64_t bits = 0;
+                for (uint32_t i = 0; i < 40 && first + i < n; i++)
+                    bits |= (uint64_t)((cur_hash[(uint64_t)(first + i) * 32 + 24] & 3u) == 0u) << i;
+                uint64_t mo = 0, mc = 0;
+                for (uint32_t o = 0; o < 9; o++) {
+                    uint32_t q = o, cnt = 0;
+                    while (q < 32 && first + q < n) {
+                        q += group_len(bits, q, n - (first + q));
+                        cnt++;
+                    }
+                    mo |= (uint64_t)(q >= 32 ? q - 32 : 0) << (4 * o);
+                    mc |= (uint64_t)cnt << (5 * o);
                 }
-                mo |= (uint64_t)(r >= 32 ? r - 32 : 0) << (4 * o);
-                mc |= (uint64_t)cnt << (5 * o);
+                s_bits[tid] = bits;
+                s_out[tid] = mo;
+                s_cnt[tid] = mc;
             }
-            s_bits[tid] = bits;
-            s_out[tid] = mo;
-            s_cnt[tid] = mc;
-        }
-        __syncthreads();
-        if (tid == 0) {  // B: compose
-            uint32_t o = 0, total = 0;
-            for (uint32_t b = 0; b < nb; b++) {
-                s_entry[b] = o;
-                s_base[b] = total;
-                total += (uint32_t)(s_cnt[b] >> (5 * o)) & 31u;
-                o = (uint32_t)(s_out[b] >> (4 * o)) & 15u;
+            __syncthreads();
+            if (tid == 0) {  // B: compose
+                uint32_t o = 0, total = 0;
+                for (uint32_t b = 0; b < nb; b++) {
+                    s_entry[b] = o;
+                    s_base[b] = total;
+                    total += (uint32_t)(s_cnt[b] >> (5 * o)) & 31u;
+                    o = (uint32_t)(s_out[b] >> (4 * o)) & 15u;
+                }
+                s_start[total] = n;
+                s_ng = total;
             }
-            s_start[total] = n;
-            s_ng = total;
+            __syncthreads();
+            if (tid < nb) {  // C: emit group starts
+                const uint32_t first = tid * 32;
+                const uint64_t bits = s_bits[tid];
+                uint32_t q = s_entry[tid], w = s_base[tid];
+                while (q < 32 && first + q < n) {
+                    s_start[w++] = first + q;
+                    q += group_len(bits, q, n - (first + q));
+                }
+            }
+            __syncthreads();
+            const uint32_t ng = s_ng;
+            for (uint32_t g = tid; g < ng; g += blockDim.x)  // D: hash the new nodes
+                hash_node_item(cur_hash, cur_size, s_start[g], s_start[g + 1] - s_start[g], nxt_hash + (uint64_t)g * 32,
+                               nxt_size + g);
+            __syncthreads();
+            uint8_t* th = cur_hash;
+            cur_hash = nxt_hash;
+            nxt_hash = th;
+            uint64_t* ts = cur_size;
+            cur_size = nxt_size;
+            nxt_size = ts;
+            n = ng;
         }
-        __syncthreads();
-        if (tid < nb) {  // C: emit group starts
-            const uint32_t first = tid * 32;
-            const uint64_t bits = s_bits[tid];
-            uint32_t r = s_entry[tid], w = s_base[tid];
-            while (r < 32 && first + r < n) {
-                s_start[w++] = first + r;
-                r += group_len(bits, r, n - (first + r));
+        // root + file hash (keyed BLAKE3 of the 32-byte root under the all-zero salt; empty file -> zero hash)
+        if (tid == 0) {
+            uint4* root = reinterpret_cast<uint4*>(a.file_root + (uint64_t)f * 32);
+            uint4* out = reinterpret_cast<uint4*>(a.file_hash + (uint64_t)f * 32);
+            if (a.file_count[f] == 0) {
+                root[0] = root[1] = out[0] = out[1] = make_uint4(0, 0, 0, 0);
+            } else {
+                if (run) {
+                    root[0] = reinterpret_cast<const uint4*>(cur_hash)[0];
+                    root[1] = reinterpret_cast<const uint4*>(cur_hash)[1];
+                }
+                const uint4 r0 = root[0], r1 = root[1];
+                uint32_t m[16] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, 0, 0, 0, 0, 0, 0, 0, 0};
+                uint32_t cv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                b3_compress(cv, m, 0u, 0u, 32u, B3_KEYED_HASH | B3_CHUNK_START | B3_CHUNK_END | B3_ROOT);
+                out[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
+                out[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
             }
         }
         __syncthreads();
-        const uint32_t ng = s_ng;
-        for (uint32_t g = tid; g < ng; g += kFinishThreads) {  // D: hash the new nodes
-            uint32_t msg[224];
-            uint64_t total;
-            const uint32_t c0 = s_start[g], c1 = s_start[g + 1];
-            const uint32_t len = format_node(cur_hash, cur_size, c0, c1 - c0, msg, &total);
-            uint32_t cv[8];
-            hash_node_message(msg, len, cv);
-            uint4* dst = reinterpret_cast<uint4*>(nxt_hash + (uint64_t)g * 32);
-            dst[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
-            dst[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
-            nxt_size[g] = total;
-        }
-        __syncthreads();
-        uint8_t* th = cur_hash;
-        cur_hash = nxt_hash;
-        nxt_hash = th;
-        uint64_t* ts = cur_size;
-        cur_size = nxt_size;
-        nxt_size = ts;
-        n = ng;
+        XG_TR();
     }
-    if (tid < 2) reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32)[tid] = reinterpret_cast<const uint4*>(cur_hash)[tid];
+#ifdef XG_MERKLE_TRACE
+    if (gtid == 0) {
+        printf("merkle trace (ns since start):");
+        for (int i = 1; i < ntr; i++) printf(" %llu", tr[i] - tr[0]);
+        printf("\n");
+    }
+#endif
 }
 
-// Level-0 node sizes are the chunk lengths.
-__global__ void merkle_init_kernel(uint64_t n_slots, const uint32_t* __restrict__ chunk_len,
-                                   uint64_t* __restrict__ node_size) {
-    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s < n_slots) node_size[s] = chunk_len[s];
+// Grid-wide barrier for a cooperative launch (every CTA is resident, which cudaLaunchCooperativeKernel guarantees):
+// a monotonically growing arrival counter; CTA-local epochs keep the word reusable without a reset.
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t& epoch, uint32_t n_blocks) {
+    __syncthreads();
+    epoch++;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        const uint32_t target = epoch * n_blocks;
+        while (*(volatile uint32_t*)counter < target) __nanosleep(32);
+        __threadfence();
+    }
+    __syncthreads();
 }
 
-// file_hash = keyed BLAKE3 of the 32-byte root under the all-zero salt; empty file -> zero hash.
-__global__ void file_hash_kernel(uint32_t n_files, const uint32_t* __restrict__ file_count,
-                                 uint8_t* __restrict__ file_root, uint8_t* __restrict__ file_hash) {
-    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= n_files) return;
-    uint4* root = reinterpret_cast<uint4*>(file_root + (uint64_t)f * 32);
-    uint4* out = reinterpret_cast<uint4*>(file_hash + (uint64_t)f * 32);
-    if (file_count[f] == 0) {
-        root[0] = root[1] = out[0] = out[1] = make_uint4(0, 0, 0, 0);
-        return;
-    }
-    const uint4 r0 = root[0], r1 = root[1];
-    uint32_t m[16] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, 0, 0, 0, 0, 0, 0, 0, 0};
-    uint32_t cv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    b3_compress(cv, m, 0u, 0u, 32u, B3_KEYED_HASH | B3_CHUNK_START | B3_CHUNK_END | B3_ROOT);
-    out[0] = make_uint4(cv[0], cv[1], cv[2], cv[3]);
-    out[1] = make_uint4(cv[4], cv[5], cv[6], cv[7]);
-}
+static int g_merkle_blocks_per_sm[64] = {};
 
 int launch_merkle(const PipelineBuffers& b, cudaStream_t st) {
     if (b.n_files == 0) return 0;
-    int n = 0;
-    const unsigned fblocks = (b.n_files + 127) / 128;
-    const unsigned sblocks = (unsigned)((b.n_slots + 127) / 128);
-    // level 0: hashes = chunk hashes (node_hash[0] aliases chunk_hash), sizes = chunk lengths
-    if (b.n_slots && b.chunk_len) {
-        merkle_init_kernel<<<(unsigned)((b.n_slots + 255) / 256), 256, 0, st>>>(b.n_slots, b.chunk_len, b.node_size[0]);
-        n++;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && g_merkle_blocks_per_sm[dev] == 0) {
+        int nb = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, merkle_coop_kernel, kMerkleThreads, 0);
+        g_merkle_blocks_per_sm[dev] = nb < 1 ? 1 : (nb > 2 ? 2 : nb);
     }
-    cudaMemcpyAsync(b.level_count[0], b.file_count, sizeof(uint32_t) * b.n_files, cudaMemcpyDeviceToDevice, st);
-    // Global level rounds while some file may still hold more than kFinishNodes nodes (host-side bound:
-    // a level of m nodes yields at most (m + 2) / 3), then one CTA per file finishes the tree.
-    int cur = 0;
-    for (uint64_t ub = b.max_nodes; ub > kFinishNodes && b.n_slots; ub = (ub + 2) / 3) {
-        merkle_block_map_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
-                                                         b.level_count[cur], b.mk_bits, b.mk_out, b.mk_cnt);
-        merkle_compose_kernel<<<(b.n_files * 32 + 127) / 128, 128, 0, st>>>(b.slot_off, b.n_files, b.node_hash[cur], b.level_count[cur],
-                                                       b.mk_out, b.mk_cnt, b.mk_entry, b.mk_base,
-                                                       b.level_count[cur ^ 1], b.group_start, b.file_root);
-        merkle_emit_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.level_count[cur], b.mk_bits,
-                                                    b.mk_entry, b.mk_base, b.group_start);
-        merkle_hash_kernel<<<sblocks, 128, 0, st>>>(b.slot_off, b.n_files, b.n_slots, b.node_hash[cur],
-                                                    b.node_size[cur], b.level_count[cur ^ 1], b.group_start,
-                                                    b.node_hash[cur ^ 1], b.node_size[cur ^ 1]);
-        n += 4;
-        cur ^= 1;
+    const unsigned per_sm = dev >= 0 && dev < 64 ? g_merkle_blocks_per_sm[dev] : 1;
+    MerkleArgs a{};
+    a.slot_off = b.slot_off;
+    a.n_files = b.n_files;
+    a.n_slots = b.n_slots;
+    a.chunk_len = b.chunk_len;
+    a.file_count = b.file_count;
+    for (int i = 0; i < 2; i++) {
+        a.node_hash[i] = b.node_hash[i];
+        a.node_size[i] = b.node_size[i];
+        a.level_count[i] = b.level_count[i];
     }
-    merkle_finish_kernel<<<b.n_files, kFinishThreads, 0, st>>>(b.slot_off, b.level_count[cur], b.node_hash[cur],
-                                                              b.node_size[cur], b.node_hash[cur ^ 1],
-                                                              b.node_size[cur ^ 1], b.file_root);
-    n++;
-    file_hash_kernel<<<fblocks, 128, 0, st>>>(b.n_files, b.file_count, b.file_root, b.file_hash);
-    return n + 1;
+    a.group_start = b.group_start;
+    a.mk_bits = b.mk_bits;
+    a.mk_out = b.mk_out;
+    a.mk_cnt = b.mk_cnt;
+    a.mk_entry = b.mk_entry;
+    a.mk_base = b.mk_base;
+    a.file_root = b.file_root;
+    a.file_hash = b.file_hash;
+    // three device words of the per-call scalar block: [0,1] round maxima, [2] barrier counter
+    uint32_t* words = reinterpret_cast<uint32_t*>(b.scalars + kScalarMerkle);
+    cudaMemsetAsync(words, 0, 16, st);
+    a.round_max = words;
+    uint32_t* barrier_word = words + 2;
+    unsigned sms = b.sm_count;
+    if (!sms) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        sms = v > 0 ? (unsigned)v : 1u;
+    }
+    unsigned grid = sms * per_sm;
+    // a grid larger than the work only adds barrier arrivals
+    const uint64_t want = std::max<uint64_t>((b.n_slots + kMerkleThreads - 1) / kMerkleThreads, b.n_files);
+    if (grid > want) grid = (unsigned)std::max<uint64_t>(want, 1);
+    void* args[] = {&a, &barrier_word};
+    launch_cooperative_gated((const void*)merkle_coop_kernel, dim3(grid), dim3(kMerkleThreads), args, 0, st);
+    return 1;
 }
 
 // ---- xorb formation -------------------------------------------------------------

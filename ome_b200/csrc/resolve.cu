@@ -358,7 +358,7 @@ __global__ void gather_kernel(const uint64_t* __restrict__ slot_off, const uint6
 
 int launch_gather(const PipelineBuffers& b, cudaStream_t st) {
     if (b.n_files == 0) return 0;
-    int n = launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial, b.scalars + kScalarChunks, st);
+    int n = 0;   // file_chunk_base / the chunk total were scanned by launch_chunk_hash
     if (b.n_slots) {
         gather_kernel<<<(unsigned)((b.n_slots + 255) / 256), 256, 0, st>>>(b.slot_off, b.file_off, b.n_files,
                                                                           b.n_slots, b.slot_end, b.chunk_len,

@@ -114,7 +114,7 @@ struct PipelineBuffers {
     cudaEvent_t ev_kernel[4];
 };
 
-enum { kScalarCand = 0, kScalarGroups = 1, kScalarChunks = 2, kScalarFlags = 3 };
+enum { kScalarCand = 0, kScalarGroups = 1, kScalarChunks = 2, kScalarFlags = 3, kScalarMerkle = 4 /* 4,5: K4's round maxima + barrier word */ };
 
 // Launchers (all asynchronous on `st`); each returns the number of kernels it launched.
 int launch_fill_splitmix(uint8_t* dst, uint64_t seed, uint64_t byte_off, uint64_t len, cudaStream_t st);
@@ -137,6 +137,12 @@ constexpr uint64_t kMaxXorbBytes = 64ull << 20;
 constexpr uint32_t kMaxXorbChunks = 8192;
 int launch_scan_u32(const uint32_t* in, uint64_t* out, uint64_t n, uint64_t* partial, uint64_t* total_out,
                     cudaStream_t st);
+
+// Cooperative kernels (grid-wide barriers) of this library never overlap one another on a device: two grids that
+// are each only partly resident would wait for CTAs that the other one's spinning CTAs keep out.  Every cooperative
+// launch goes through this gate, which chains it behind the previous one on the same device with an event (any
+// stream, any context of this process).  Bulk kernels are not affected.
+cudaError_t launch_cooperative_gated(const void* kernel, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t st);
 
 inline uint64_t scan_blocks(uint64_t n) { return (n + 2047) / 2048; }
 
