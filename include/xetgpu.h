@@ -95,8 +95,10 @@ typedef struct {
     uint64_t staging_bytes;     /* size of EACH of the two pinned host staging buffers used to copy
                                    pageable host memory; 0 = 64 MiB.  xetgpu_hash_files reads through a ring
                                    of 16 pinned slots of min(staging_bytes, 64 MiB) each (16 MiB when 0) */
-    uint64_t max_batch_bytes;   /* xetgpu_hash_files: bytes resident on the device per batch;
-                                   0 = 8 GiB */
+    uint64_t max_batch_bytes;   /* xetgpu_hash_files: bytes resident on the device per batch; 0 = 8 GiB.
+                                   A single file larger than this streams through the device in pieces of this
+                                   size (byte ranges with the carried cut, combined at the end), so device memory
+                                   stays bounded whatever the file size; xorbs are not formed for such a file */
     uint32_t flags;             /* XETGPU_CTX_* */
 } XetGpuConfig;
 

@@ -1236,6 +1236,8 @@ struct FileProgress {
     std::atomic<uint64_t>* shared_bytes = nullptr;  // multi-device: bytes completed by all devices together
     std::atomic<uint32_t>* shared_files = nullptr;  // multi-device: files completed by all devices together
     XetProgressUpdate pu{};
+    uint64_t base_bytes = 0;              // single-device: bytes of the batches / pieces already read
+    uint64_t skip_bytes = 0;              // bytes of the current read that are a range's lead (not counted as progress)
 };
 
 // Reads byte ranges of files into c->d_input through the reader pool.  Caller holds the context.
@@ -1247,7 +1249,7 @@ struct FileSpan {
 
 static XetError* read_spans_to_device(XetGpuContext* c, const char* const* paths, const std::vector<FileSpan>& spans,
                                       std::vector<uint64_t>* rel, const XetCancellationToken* cancel,
-                                      FileProgress* prog, uint64_t bytes_before) {
+                                      FileProgress* prog) {
     uint64_t bytes = 0;
     for (const auto& sp : spans) bytes += sp.len;
     if (XetError* e = ensure_input(c, bytes)) return e;
@@ -1271,12 +1273,13 @@ static XetError* read_spans_to_device(XetGpuContext* c, const char* const* paths
     uint64_t reported = 0;
     return run_reader_pool(c, pool, [&](ReaderPool& pl) {
         if (prog && prog->report_to) {
-            const uint64_t done = pl.bytes_done.load();
+            const uint64_t raw = pl.bytes_done.load();
+            const uint64_t done = raw > prog->skip_bytes ? raw - prog->skip_bytes : 0;
             if (prog->shared_bytes) {
                 prog->pu.completed_bytes = prog->shared_bytes->fetch_add(done - reported) + (done - reported);
                 reported = done;
             } else {
-                prog->pu.completed_bytes = bytes_before + done;
+                prog->pu.completed_bytes = prog->base_bytes + done;
             }
             prog->pu.current_file = paths[pl.last_file.load()];
             report_progress(prog->report_to, prog->pu, false);
@@ -1285,18 +1288,70 @@ static XetError* read_spans_to_device(XetGpuContext* c, const char* const* paths
     });
 }
 
-// Hash whole files (paths[idx[k]] for k in [0, n)) on context c, batch by batch.  Results land in files_out[idx[k]]
-// and, with want_chunks, in the per-file chunk vectors.  Caller holds the context.
+struct MultiPiece {
+    size_t file;
+    uint64_t begin, end, file_len;
+    bool whole() const { return begin == 0 && end == file_len; }
+};
+
+// Port of sharded.plan_concatenated: per device, its pieces in file order.
+// One owner's chunk list for its range of a shared file.
+struct RangePart {
+    std::vector<uint64_t> ends;     // file-relative
+    std::vector<uint8_t> hashes;
+    uint64_t exit_cut = 0;
+};
+
+static XetError* hash_file_range_locked(XetGpuContext* c, const char* const* paths, const MultiPiece& p, uint64_t end,
+                                        uint64_t entry_cut, const XetCancellationToken* cancel, FileProgress* prog,
+                                        RangePart* out);
+static XetError* merkle_from_chunks_locked(XetGpuContext* c, const uint8_t* chunk_hashes, const uint64_t* chunk_sizes,
+                                           uint64_t n_chunks, uint8_t out_merkle_root[32], uint8_t out_file_hash[32]);
 struct FileChunks {
     std::vector<uint64_t> ends;
     std::vector<uint8_t> hashes;
 };
 
+// A file larger than max_batch_bytes never sits on the device whole: it streams through in pieces of that size.
+// Piece k holds bytes [begin_k - RANGE_LEAD, end_k) and is hashed as a byte range whose entry cut is the exit cut
+// of piece k - 1 (exact, no speculation: the pieces run in order), and the chunk lists are combined at the end.
+static XetError* hash_large_file_streaming(XetGpuContext* c, const char* const* paths, size_t f, uint64_t size,
+                                           const XetCancellationToken* cancel, FileProgress* prog,
+                                           XetGpuFileResult* out, std::vector<uint64_t>* ends_out,
+                                           std::vector<uint8_t>* hashes_out) {
+    const uint64_t piece = std::max<uint64_t>(c->max_batch_bytes / 4096 * 4096, 1ull << 20);
+    std::vector<uint64_t> ends;
+    std::vector<uint8_t> hashes;
+    uint64_t entry = 0;
+    for (uint64_t begin = 0; begin < size; begin += piece) {
+        const uint64_t end = std::min<uint64_t>(size, begin + piece);
+        RangePart part;
+        if (XetError* e = hash_file_range_locked(c, paths, MultiPiece{f, begin, end, size}, end, entry, cancel, prog, &part))
+            return e;
+        ends.insert(ends.end(), part.ends.begin(), part.ends.end());
+        hashes.insert(hashes.end(), part.hashes.begin(), part.hashes.end());
+        entry = part.exit_cut;
+        if (prog) prog->base_bytes += end - begin;
+    }
+    std::vector<uint64_t> csz(ends.size());
+    for (size_t i = 0; i < csz.size(); i++) csz[i] = ends[i] - (i ? ends[i - 1] : 0);
+    *out = XetGpuFileResult{};
+    out->size = size;
+    out->n_chunks = ends.size();
+    if (XetError* e = merkle_from_chunks_locked(c, hashes.data(), csz.data(), csz.size(), out->merkle_root, out->file_hash))
+        return e;
+    if (ends_out) *ends_out = std::move(ends);
+    if (hashes_out) *hashes_out = std::move(hashes);
+    return nullptr;
+}
+
+// Hash whole files (paths[idx[k]] for k in [0, n)) on context c, batch by batch.  Results land in files_out[idx[k]]
+// and, with want_chunks, in the per-file chunk vectors.  Caller holds the context.
+
 static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, const std::vector<size_t>& idx,
                                   const std::vector<uint64_t>& sizes, bool want_chunks, const XetCancellationToken* cancel,
                                   FileProgress* prog, XetGpuFileResult* files_out, std::vector<FileChunks>* chunks_out,
                                   std::vector<XetGpuXorb>* xorbs_out = nullptr) {
-    uint64_t bytes_before = 0;
     size_t k0 = 0;
     while (k0 < idx.size()) {
         // batch = as many whole files as fit in max_batch_bytes (at least one)
@@ -1304,14 +1359,31 @@ static XetError* hash_whole_files(XetGpuContext* c, const char* const* paths, co
         uint64_t bytes = 0;
         while (k1 < idx.size() && (k1 == k0 || bytes + sizes[idx[k1]] <= c->max_batch_bytes)) bytes += sizes[idx[k1++]];
         if (cancelled(cancel)) return make_error(XETGPU_ERR_CANCELLED, "cancelled");
+        if (k1 == k0 + 1 && sizes[idx[k0]] > c->max_batch_bytes && sizes[idx[k0]] > (1ull << 20)) {
+            // one file beyond the device budget: stream it (xorbs are not formed for such a file)
+            const size_t f = idx[k0];
+            FileChunks* fc = want_chunks && chunks_out ? &(*chunks_out)[f] : nullptr;
+            if (XetError* e = hash_large_file_streaming(c, paths, f, sizes[f], cancel, prog, &files_out[f],
+                                                        fc ? &fc->ends : nullptr, fc ? &fc->hashes : nullptr))
+                return e;
+            if (prog && prog->report_to && !prog->shared_bytes) {
+                prog->pu.completed_bytes = prog->base_bytes;
+                prog->pu.completed_files = (uint32_t)k1;
+                report_progress(prog->report_to, prog->pu, false);
+            } else if (prog && prog->shared_files) {
+                prog->shared_files->fetch_add(1);
+            }
+            k0 = k1;
+            continue;
+        }
         std::vector<FileSpan> spans;
         for (size_t k = k0; k < k1; k++) spans.push_back(FileSpan{idx[k], 0, sizes[idx[k]], sizes[idx[k]]});
         std::vector<uint64_t> rel;
-        if (XetError* e = read_spans_to_device(c, paths, spans, &rel, cancel, prog, bytes_before)) return e;
-        bytes_before += bytes;
+        if (XetError* e = read_spans_to_device(c, paths, spans, &rel, cancel, prog)) return e;
+        if (prog) prog->base_bytes += bytes;
         if (prog && prog->report_to) {
             if (!prog->shared_bytes) {
-                prog->pu.completed_bytes = bytes_before;
+                prog->pu.completed_bytes = prog->base_bytes;
                 prog->pu.completed_files = (uint32_t)k1;
             } else if (prog->shared_files) {
                 prog->pu.completed_files = prog->shared_files->fetch_add((uint32_t)(k1 - k0)) + (uint32_t)(k1 - k0);
@@ -1579,6 +1651,11 @@ extern "C" XetError* xetgpu_merkle_from_chunks(XetGpuContext* c, const uint8_t* 
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_merkle_from_chunks");
     LOCK_CTX(c);
     CU(cudaSetDevice(c->device));
+    return merkle_from_chunks_locked(c, chunk_hashes, chunk_sizes, n_chunks, out_merkle_root, out_file_hash);
+}
+
+static XetError* merkle_from_chunks_locked(XetGpuContext* c, const uint8_t* chunk_hashes, const uint64_t* chunk_sizes,
+                                           uint64_t n_chunks, uint8_t out_merkle_root[32], uint8_t out_file_hash[32]) {
     // a one-file plan whose slot range holds exactly n_chunks nodes
     Plan plan;
     plan.total = 0;
@@ -1647,13 +1724,6 @@ struct XetGpuMulti {
     uint64_t min_bytes_per_device = 64ull << 20;  // below this much work per device, fewer devices are used
 };
 
-struct MultiPiece {
-    size_t file;
-    uint64_t begin, end, file_len;
-    bool whole() const { return begin == 0 && end == file_len; }
-};
-
-// Port of sharded.plan_concatenated: per device, its pieces in file order.
 // Nearest tensor boundary of a *.safetensors shard to `off`, if one lies within a quarter range and leaves both
 // neighbours room for the halo; `off` itself otherwise (other file types, unparsable headers, giant tensors).
 static uint64_t snap_to_tensor(const char* path, uint64_t size, uint64_t off, uint64_t range_bytes) {
@@ -1772,13 +1842,6 @@ extern "C" XetError* xetgpu_multi_set_progress_callback(XetGpuMulti* m, XetProgr
     return xetgpu_context_set_progress_callback(m->ctx[0], callback, user_data, throttle_ms);  // one handler, one throttle
 }
 
-// One owner's chunk list for its range of a shared file.
-struct RangePart {
-    std::vector<uint64_t> ends;     // file-relative
-    std::vector<uint8_t> hashes;
-    uint64_t exit_cut = 0;
-};
-
 // Caller holds c.  Reads [begin - lead, end) of the file and hashes the range from entry_cut.
 static XetError* hash_file_range_locked(XetGpuContext* c, const char* const* paths, const MultiPiece& p, uint64_t end,
                                         uint64_t entry_cut, const XetCancellationToken* cancel, FileProgress* prog,
@@ -1787,7 +1850,10 @@ static XetError* hash_file_range_locked(XetGpuContext* c, const char* const* pat
     const uint64_t data_pos = p.begin - lead;
     std::vector<FileSpan> spans{FileSpan{p.file, data_pos, end - data_pos, p.file_len}};
     std::vector<uint64_t> rel;
-    if (XetError* e = read_spans_to_device(c, paths, spans, &rel, cancel, prog, 0)) return e;
+    if (prog) prog->skip_bytes = lead;
+    XetError* re = read_spans_to_device(c, paths, spans, &rel, cancel, prog);
+    if (prog) prog->skip_bytes = 0;
+    if (re) return re;
     uint64_t offsets[2] = {0, end - data_pos};
     RangeWalk rw{entry_cut - data_pos, end == p.file_len ? 1u : 0u};
     RunOptions opt;

@@ -167,3 +167,23 @@ def test_shared_safetensors_shard_is_cut_on_tensor_boundaries(tmp_path, monkeypa
         assert raw_cuts != cuts and all(c % 4096 == 0 for c in raw_cuts)
         cl = m.hash_files([str(p), str(other)], want_chunks=True)
     _check(cl, [data, np.frombuffer(b"{}", dtype=np.uint8)])
+
+
+def test_file_larger_than_the_device_budget_streams_in_pieces(tmp_path):
+    """max_batch_bytes bounds device memory: a bigger file is hashed piece by piece (byte ranges, carried cut)."""
+    import ome_b200
+    specs = [[["splitmix", 49, (40 << 20) + 4321]], [["splitmix", 50, 3 << 20]], [["zeros", 20 << 20]], []]
+    paths, datas = _write(tmp_path, specs)
+    h = ome_b200.XetHasher(max_batch_bytes=8 << 20)
+    try:
+        seen = []
+        h.set_progress_handler(seen.append, throttle_ms=0)
+        cl = h.hash_files(paths, want_chunks=True)
+        h.set_progress_handler(None)
+        _check(cl, datas)
+        done = [u["completed_bytes"] for u in seen]
+        assert done == sorted(done) and done[-1] == sum(d.size for d in datas)
+        _check(h.hash_files(paths), datas)
+        h.verify_file(paths[0], cl.files[0].hex)
+    finally:
+        h.close()

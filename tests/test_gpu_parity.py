@@ -505,7 +505,7 @@ def test_xorb_formation_matches_oracle(hasher, tmp_path):
         p = tmp_path / f"x{i}.bin"
         d.tofile(p)
         paths.append(str(p))
-    small = __import__("ome_b200").XetHasher(max_batch_bytes=100 << 20)   # several batches: file indices are remapped
+    small = __import__("ome_b200").XetHasher(max_batch_bytes=200 << 20)   # two batches: file indices are remapped
     try:
         cl2 = small.hash_files(paths, want_xorbs=True)
     finally:
