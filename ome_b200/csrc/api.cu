@@ -84,6 +84,10 @@ struct Arena {
     }
 };
 
+constexpr size_t kReadSlotsDefault = 16;  // pinned 16 MiB slots of the file reader ring (XETGPU_READ_SLOTS overrides; measured on B200:
+                                          // 16, 32 and 64 slots x 16 or 32 threads all read tmpfs at 42-45 GB/s — the host memory system is the bound)
+constexpr size_t kReadThreadsMax = 16;
+
 struct XetGpuContext {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -121,6 +125,7 @@ struct XetGpuContext {
     std::vector<cudaEvent_t> read_slot_ev;
     uint64_t read_slot_bytes = 16ull << 20;
     size_t read_threads = 8;
+    size_t n_read_slots = kReadSlotsDefault;
     uint64_t cand_cap_hint = 0;
     XetGpuTimings last = {};
     // progress
@@ -156,7 +161,7 @@ struct CtxGuard {
     return make_error(XETGPU_ERR_INVALID_CONFIG, "re-entrant call: a progress or cancellation callback " \
                                                  "called a hashing entry point of the context that is running it")
 
-constexpr size_t kReadSlots = 16;  // pinned 16 MiB slots of the file reader ring
+
 
 typedef XetGpuContext::Lane Lane;
 
@@ -244,7 +249,11 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
     }
     {
         unsigned hc = std::thread::hardware_concurrency();
-        c->read_threads = hc ? std::min<size_t>(kReadSlots, hc) : 4;
+        c->read_threads = hc ? std::min<size_t>(kReadThreadsMax, hc) : 4;
+        if (const char* v = getenv("XETGPU_READ_SLOTS")) {
+            unsigned long n = strtoul(v, nullptr, 10);
+            if (n) c->n_read_slots = std::min<size_t>(std::max<size_t>(n, 2), 256);
+        }
         if (const char* v = getenv("XETGPU_READ_THREADS")) {
             unsigned long n = strtoul(v, nullptr, 10);
             if (n) c->read_threads = std::min<size_t>(n, 64);
@@ -615,8 +624,8 @@ struct ReaderPool {
 };
 
 static XetError* ensure_read_slots(XetGpuContext* c) {
-    if (c->read_slots.size() == kReadSlots) return nullptr;
-    for (size_t i = c->read_slots.size(); i < kReadSlots; i++) {
+    if (c->read_slots.size() == c->n_read_slots) return nullptr;
+    for (size_t i = c->read_slots.size(); i < c->n_read_slots; i++) {
         uint8_t* p = nullptr;
         CU(cudaMallocHost((void**)&p, c->read_slot_bytes));
         cudaEvent_t ev;
@@ -634,9 +643,10 @@ static XetError* run_reader_pool(XetGpuContext* c, ReaderPool& pool, Poll poll) 
     pool.c = c;
     pool.slots = c->read_slots;
     pool.slot_ev = c->read_slot_ev;
-    pool.slot_issued.assign(kReadSlots, -1);
-    for (size_t s = 0; s < kReadSlots; s++) pool.slot_issued[s] = (long)s - (long)kReadSlots;
-    const size_t nthreads = std::min<size_t>(std::min<size_t>(c->read_threads, pool.pieces.size()), kReadSlots);
+    const size_t S = c->n_read_slots;
+    pool.slot_issued.assign(S, -1);
+    for (size_t s = 0; s < S; s++) pool.slot_issued[s] = (long)s - (long)S;
+    const size_t nthreads = std::min<size_t>(std::min<size_t>(c->read_threads, pool.pieces.size()), S);
     std::vector<std::thread> threads;
     for (size_t t = 0; t < nthreads; t++) threads.emplace_back([&pool] { pool.worker(); });
     while (pool.next.load() < pool.pieces.size() && !pool.stop) {
