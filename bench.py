@@ -843,8 +843,7 @@ def leg_config4(cx: Ctx):
     ms = cx.timed(lambda: step(phases), steps, 1)
     # phases hold host wall-clock sums over warm-up + timed steps on this rank; report the slowest rank's per-step means
     # (a fixed key list keeps the reductions identical on every rank: a rank without a shared shard has no such phases)
-    keys = ("whole_files_ms", "halo_exchange_ms", "speculative_pass_ms", "carry_chain_ms", "gather_ms", "merkle_ms",
-            "result_allreduce_ms")
+    keys = ("halo_exchange_ms", "batched_pass_ms", "carry_chain_ms", "gather_ms", "merkle_ms", "result_allreduce_ms")
     ph = {k: cx.max_over_ranks(phases.get(k, 0.0) / (steps + 1)) for k in keys}
     rehashed = int(cx.max_over_ranks(float(state["rehashed"])))
     hasher.close()

@@ -260,6 +260,24 @@ XetError* xetgpu_hash_range(XetGpuContext* ctx, const void* data, int32_t memory
                             uint64_t* out_exit_cut, XetGpuResult** out_result);
 
 /*
+ * Whole files and byte-range items in ONE batched call — what a rank of a byte-range partitioned job holds: the
+ * files that lie inside its range plus its pieces of the files it shares with its neighbours (BASELINE config 4).
+ * Item i is data[offsets[i] .. offsets[i+1]) and is described by specs[i]; a whole file is {len, 0, len, 0}, a
+ * byte-range item has the meaning of xetgpu_hash_range's arguments (its data starts `lead` bytes before
+ * range_begin).  XETGPU_WANT_CHUNKS is required.  Per item the result holds the chunk list (ends relative to the
+ * FILE) and, for whole files, root and file hash (for byte-range items those two fields cover only the item's own
+ * chunks and are not a file's); out_exit_cuts[i] (optional) receives the cut to hand to the next range's owner.
+ */
+typedef struct {
+    uint64_t file_len;
+    uint64_t range_begin, range_end;
+    uint64_t entry_cut;
+} XetGpuRangeSpec;
+XetError* xetgpu_hash_buffers_ranges(XetGpuContext* ctx, const void* data, const uint64_t* offsets, size_t n_items,
+                                     int32_t memory, uint32_t flags, const XetGpuRangeSpec* specs,
+                                     uint64_t* out_exit_cuts, XetGpuResult** out_result);
+
+/*
  * Boundary resolution is a carry chain across ranges; to keep ranks from waiting on one
  * another, a range owner may first ask for the cut it WOULD hand on if its own entry were
  * `assumed_entry_cut`, forward that, and only re-run when the true entry differs.

@@ -50,6 +50,10 @@ class XetGpuResult(C.Structure):
                 ("n_xorbs", C.c_uint64), ("xorbs", C.POINTER(XetGpuXorb))]
 
 
+class XetGpuRangeSpec(C.Structure):
+    _fields_ = [("file_len", C.c_uint64), ("range_begin", C.c_uint64), ("range_end", C.c_uint64), ("entry_cut", C.c_uint64)]
+
+
 class XetGpuTensorInfo(C.Structure):
     _fields_ = [("name", C.c_char_p), ("dtype", C.c_char_p), ("begin", C.c_uint64), ("end", C.c_uint64),
                 ("n_elements", C.c_uint64), ("rank", C.c_uint32)]
@@ -79,6 +83,9 @@ SIGNATURES = {
     "xetgpu_context_set_progress_callback": (ERRP, [CTX, ProgressCallback, C.c_void_p, C.c_uint32]),
     "xetgpu_hash_buffers": (ERRP, [CTX, C.c_void_p, C.POINTER(C.c_uint64), C.c_size_t, C.c_int32, C.c_uint32,
                                    C.POINTER(C.POINTER(XetGpuResult))]),
+    "xetgpu_hash_buffers_ranges": (ERRP, [CTX, C.c_void_p, C.POINTER(C.c_uint64), C.c_size_t, C.c_int32, C.c_uint32,
+                                          C.POINTER(XetGpuRangeSpec), C.POINTER(C.c_uint64),
+                                          C.POINTER(C.POINTER(XetGpuResult))]),
     "xetgpu_hash_files": (ERRP, [CTX, C.POINTER(C.c_char_p), C.c_size_t, C.c_uint32,
                                  C.POINTER(XetCancellationToken), C.POINTER(C.POINTER(XetGpuResult))]),
     "xetgpu_verify_file": (ERRP, [CTX, C.c_char_p, C.c_char_p]),

@@ -84,6 +84,10 @@ struct Arena {
     }
 };
 
+// A lane is a workspace + pinned metadata + timing events; lanes alternate between TWO streams.  A batch of several
+// file groups gives every group its own lane, so the host enqueues all groups without waiting for any of them and
+// collects the results at the end (round 1 had two lanes and had to drain group g before it could launch g + 2).
+constexpr int kMaxLanes = 8;
 constexpr size_t kReadSlotsDefault = 16;  // pinned 16 MiB slots of the file reader ring (XETGPU_READ_SLOTS overrides; measured on B200:
                                           // 16, 32 and 64 slots x 16 or 32 threads all read tmpfs at 42-45 GB/s — the host memory system is the bound)
 constexpr size_t kReadThreadsMax = 16;
@@ -111,9 +115,10 @@ struct XetGpuContext {
         uint64_t h_chunks_cap = 0;
         cudaEvent_t ev[8] = {};
         cudaEvent_t ev_kernel[4] = {};
-    } lanes[2];
+    } lanes[kMaxLanes];
+    cudaStream_t second_stream = nullptr;  // odd lanes launch here, even lanes on `stream`
     cudaEvent_t ev_fork = nullptr;
-    cudaEvent_t ev_gear_done[2] = {nullptr, nullptr};
+    cudaEvent_t ev_gear_done[kMaxLanes] = {};
     int force_lanes = -1;  // XETGPU_TWO_LANES=0/1 overrides the two-lane policy (experiments)
     uint64_t min_group_bytes = 256ull << 20;  // smallest file group worth its own lane (XETGPU_MIN_GROUP_BYTES)
     uint8_t* d_input = nullptr;  // device copy of host inputs
@@ -224,8 +229,8 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
     if (!c->stream) {
         if (ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking))) c->own_stream = true;
     }
-    c->lanes[0].stream = c->stream;
-    ok(cudaStreamCreateWithFlags(&c->lanes[1].stream, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&c->second_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < kMaxLanes; k++) c->lanes[k].stream = (k & 1) ? c->second_stream : c->stream;
     for (auto& l : c->lanes) {
         for (auto& ev : l.ev) ok(cudaEventCreate(&ev));
         for (auto& ev : l.ev_kernel) ok(cudaEventCreate(&ev));
@@ -277,7 +282,10 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
         for (auto& ev : l.ev_kernel)
             if (ev) cudaEventDestroy(ev);
     }
-    if (c->lanes[1].stream) cudaStreamDestroy(c->lanes[1].stream);
+    if (c->second_stream) {
+        cudaStreamSynchronize(c->second_stream);
+        cudaStreamDestroy(c->second_stream);
+    }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (auto& ev : c->ev_gear_done)
         if (ev) cudaEventDestroy(ev);
@@ -365,6 +373,7 @@ struct Plan {
     std::vector<uint64_t> slot_off;  // host prefix
     std::vector<uint64_t> seg_off;   // host prefix of per-file segment counts (K2)
     uint64_t n_segs = 0;
+    bool has_items = false;          // the batch carries per-file byte-range descriptors (RunOptions::items)
     std::vector<uint64_t> xorb_off;  // host prefix of per-file xorb upper bounds (only with want_xorbs)
     uint64_t n_xorb_slots = 0;
 };
@@ -429,6 +438,8 @@ static XetError* carve(Lane* l, const Plan& p, PipelineBuffers* b, bool dry, uin
     b->max_nodes = p.max_nodes;
     b->total_bytes = p.total;
     b->file_off = a.take<uint64_t>(F + 1);
+    uint64_t* walk = a.take<uint64_t>(F + 1);
+    b->file_walk = p.has_items ? walk : nullptr;
     b->slot_off = a.take<uint64_t>(F + 1);
     b->tile_count = a.take<uint32_t>(T + 1);
     b->tile_stage = a.take<uint32_t>(T * (uint64_t)kGearCap + 1);
@@ -722,6 +733,15 @@ struct RunOptions {
     bool resolve_only = false;         // stop after K2 (range exit-cut query)
     uint64_t* exit_cut_abs = nullptr;  // resolve_only / range: last cut (absolute in data), or walk_start if none
     bool skip_merkle = false;
+    // A batch that mixes whole files and byte-range items (xetgpu_hash_buffers_ranges): per item, the position in its
+    // own data of the entry cut, whether the data ends at the end of the file, and the file position of data[0].
+    struct Item {
+        uint64_t walk_rel;   // entry cut, relative to the item's first data byte
+        bool is_eof;
+        uint64_t bias;       // file position of the item's first data byte (added to the chunk ends returned)
+    };
+    const std::vector<Item>* items = nullptr;
+    std::vector<uint64_t>* item_exit_cuts = nullptr;   // per item: last cut (file position), or the entry cut if none
 };
 
 // One group of files in flight on a lane: everything launch_group enqueued and finish_group reads.
@@ -757,6 +777,7 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
     g->n_files = n_files;
     const bool xorbs = opt.want_xorbs && !opt.resolve_only && !opt.skip_merkle;
     g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint, xorbs);
+    g->plan.has_items = opt.items != nullptr;
     const Plan& plan = g->plan;
     PipelineBuffers& b = g->b;
     b = PipelineBuffers{};
@@ -767,12 +788,16 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
     // metadata upload through pinned memory
     const uint64_t F = n_files;
     const uint64_t X = plan.n_xorb_slots;
-    const uint64_t meta_bytes = (F + 1) * 24 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256 +
+    const uint64_t meta_bytes = (F + 1) * 32 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256 +
                                 (xorbs ? (F + 1) * 8 + (F + 2) * 4 + (X + 1) * (8 + 8 + 4 + 32) + 64 : 0);
     if (XetError* e = ensure_meta(lane, meta_bytes)) return e;
     uint64_t* h_off = reinterpret_cast<uint64_t*>(lane->h_meta);
     uint64_t* h_slot = h_off + (F + 1);
     uint64_t* h_seg = h_slot + (F + 1);
+    uint64_t* h_walk = h_seg + (F + 1);
+    if (opt.items)
+        for (size_t f = 0; f < F; f++)
+            h_walk[f] = (offsets[f] + (*opt.items)[f].walk_rel) | ((*opt.items)[f].is_eof ? 0ull : 1ull << 63);
     memcpy(h_off, offsets, (F + 1) * 8);
     memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
     memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
@@ -782,6 +807,7 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
     CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (opt.items && F) CU(cudaMemcpyAsync((void*)b.file_walk, h_walk, F * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(b.scalars, 0, 64, st));
     b.sm_count = c->sm_count;
     cudaError_t gear_err = cudaSuccess;
@@ -816,7 +842,7 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
     }
     CU(cudaGetLastError());
     // readback: scalars, per-file counts, bases, roots, hashes
-    uint8_t* h_rb = lane->h_meta + (F + 1) * 24;
+    uint8_t* h_rb = lane->h_meta + (F + 1) * 32;
     g->h_scalars = reinterpret_cast<uint64_t*>(h_rb);
     g->h_base = g->h_scalars + 8;
     g->h_count = reinterpret_cast<uint32_t*>(g->h_base + (F + 2));
@@ -936,6 +962,20 @@ static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const
         if (!opt.resolve_only) memcpy(rb->hashes.data() + chunk0 * 32, ph, n_chunks * 32);
         if (opt.end_bias)
             for (uint64_t i = 0; i < n_chunks; i++) rb->ends[chunk0 + i] += opt.end_bias;
+        if (opt.items)
+            for (size_t f = 0; f < F; f++) {
+                const uint64_t bias = (*opt.items)[f].bias;
+                const uint64_t c0 = chunk0 + g->h_base[f], c1 = c0 + g->h_count[f];
+                for (uint64_t i = c0; i < c1; i++) rb->ends[i] += bias;
+            }
+    }
+    if (opt.items && opt.item_exit_cuts) {
+        opt.item_exit_cuts->assign(F, 0);
+        for (size_t f = 0; f < F; f++) {
+            const RunOptions::Item& it = (*opt.items)[f];
+            const uint64_t c1 = chunk0 + g->h_base[f] + g->h_count[f];
+            (*opt.item_exit_cuts)[f] = g->h_count[f] && opt.want_chunks ? rb->ends[c1 - 1] : it.bias + it.walk_rel;
+        }
     }
     if (timing) {
         cudaEventRecord(lane->ev[6], st);
@@ -1064,6 +1104,7 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
     // each fill the SMs' shared memory, so they cannot be co-resident anyway).
     bool two_lanes = !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && (host.base != nullptr || n_files >= 16);
     if (c->force_lanes >= 0 && !opt.range) two_lanes = c->force_lanes == 1;
+    if (opt.items) two_lanes = false;   // per-item descriptors are indexed by position in the batch: one group
     if (two_lanes) {
         uint64_t acc = 0;
         for (size_t f = 0; f < n_files; f++) {
@@ -1097,13 +1138,17 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
             if (attempt == 2) return make_error(XETGPU_ERR_UNKNOWN, "candidate list kept overflowing");
         }
     } else {
-        // lane 1 must see what the caller enqueued on the context's stream before this call
+        // the second stream must see what the caller enqueued on the context's stream before this call
         CU(cudaEventRecord(c->ev_fork, c->stream));
-        CU(cudaStreamWaitEvent(c->lanes[1].stream, c->ev_fork, 0));
-        GroupState state[2];
-        std::vector<uint64_t> rel[2];
-        uint64_t group_base[2] = {0, 0};
-        long pending[2] = {-1, -1};
+        CU(cudaStreamWaitEvent(c->second_stream, c->ev_fork, 0));
+        // Group gi runs on lane gi % kMaxLanes (its own workspace and pinned metadata; streams alternate), so every
+        // group is enqueued without waiting for an earlier one; a lane is drained only when a batch has more groups
+        // than lanes.  Results are collected in group order at the end.
+        std::vector<GroupState> state(kMaxLanes);
+        std::vector<std::vector<uint64_t>> rel(kMaxLanes);
+        uint64_t group_base[kMaxLanes] = {};
+        long pending[kMaxLanes];
+        for (auto& x : pending) x = -1;
         auto finish = [&](int li) -> XetError* {
             if (pending[li] < 0) return nullptr;
             const size_t gi = (size_t)pending[li];
@@ -1115,11 +1160,13 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
                                       cut[gi + 1] - cut[gi], opt, &rb);
             return nullptr;
         };
+        size_t next_finish = 0;   // groups finish in order: results are appended in group order
         for (size_t gi = 0; gi < G; gi++) {
-            const int li = (int)(gi & 1);
-            // results are collected in group order: the other lane's older group first
-            if (gi >= 2)
-                if (XetError* e = finish(li)) return e;
+            const int li = (int)(gi % kMaxLanes);
+            while (gi - next_finish >= (size_t)kMaxLanes) {
+                if (XetError* e = finish((int)(next_finish % kMaxLanes))) return e;
+                next_finish++;
+            }
             const size_t f0 = cut[gi], f1 = cut[gi + 1];
             // the group's device base must stay 16-byte aligned (TMA): start it at the aligned address at or
             // below its first file; the few bytes of the previous file in front are ignored by every kernel
@@ -1129,14 +1176,14 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
             for (size_t f = f0; f <= f1; f++) rel[li][f - f0] = offsets[f] - base_lo;
             state[li] = GroupState{};
             if (XetError* e = ingest(&c->lanes[li], offsets[f0], offsets[f1], &state[li])) return e;
+            const int prev = (int)((gi + kMaxLanes - 1) % kMaxLanes);
             if (XetError* e = launch_group(c, &c->lanes[li], d_data + base_lo, rel[li].data(), f1 - f0, opt, &state[li],
-                                           gi ? c->ev_gear_done[li ^ 1] : nullptr, c->ev_gear_done[li]))
+                                           gi ? c->ev_gear_done[prev] : nullptr, c->ev_gear_done[li]))
                 return e;
             pending[li] = (long)gi;
         }
-        const int first = pending[0] >= 0 && (pending[1] < 0 || pending[0] < pending[1]) ? 0 : 1;
-        if (XetError* e = finish(first)) return e;
-        if (XetError* e = finish(first ^ 1)) return e;
+        for (; next_finish < G; next_finish++)
+            if (XetError* e = finish((int)(next_finish % kMaxLanes))) return e;
     }
     float wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     publish_timings(c, rb, total, wall);
@@ -1223,6 +1270,56 @@ extern "C" XetError* xetgpu_hash_buffers(XetGpuContext* c, const void* data, con
     opt.want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;
     opt.want_xorbs = (flags & XETGPU_WANT_XORBS) != 0;
     return run_batch(c, d, host, rel.data(), n_files, opt, out_result);
+}
+
+// Whole files and byte-range items in ONE batch (the config-4 rank: its whole shards plus its pieces of the two
+// shards it shares).  Item i is data[offsets[i] .. offsets[i+1]) = bytes [range_begin - lead, range_end) of a file of
+// file_len bytes, lead = min(range_begin, XETGPU_RANGE_LEAD); a whole file is {len, 0, len, 0}.
+extern "C" XetError* xetgpu_hash_buffers_ranges(XetGpuContext* c, const void* data, const uint64_t* offsets, size_t n_items,
+                                                int32_t memory, uint32_t flags, const XetGpuRangeSpec* specs,
+                                                uint64_t* out_exit_cuts, XetGpuResult** out_result) {
+    if (!c || !out_result || (n_items && (!offsets || !specs)))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_hash_buffers_ranges");
+    *out_result = nullptr;
+    if (!(flags & XETGPU_WANT_CHUNKS))
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "xetgpu_hash_buffers_ranges needs XETGPU_WANT_CHUNKS: a byte-range item's "
+                                                     "result IS its chunk list");
+    std::vector<RunOptions::Item> items(n_items);
+    for (size_t i = 0; i < n_items; i++) {
+        const XetGpuRangeSpec& sp = specs[i];
+        if (offsets[i + 1] < offsets[i]) return make_error(XETGPU_ERR_INVALID_CONFIG, "offsets must be ascending");
+        if (sp.range_begin > sp.range_end || sp.range_end > sp.file_len || sp.entry_cut > sp.range_begin)
+            return make_error(XETGPU_ERR_INVALID_CONFIG, "need entry_cut <= range_begin <= range_end <= file_len");
+        const uint64_t lead = std::min<uint64_t>(sp.range_begin, XETGPU_RANGE_LEAD);
+        const uint64_t data_pos = sp.range_begin - lead;
+        if (sp.entry_cut < data_pos || sp.range_begin - sp.entry_cut > XETGPU_MAX_CHUNK)
+            return make_error(XETGPU_ERR_INVALID_CONFIG, "entry_cut must lie within one maximum chunk before range_begin");
+        if (offsets[i + 1] - offsets[i] != sp.range_end - data_pos)
+            return make_error(XETGPU_ERR_INVALID_CONFIG, "an item's data must be bytes [range_begin - lead, range_end) of its file");
+        items[i] = RunOptions::Item{sp.entry_cut - data_pos, sp.range_end == sp.file_len, data_pos};
+    }
+    if (n_items && offsets[n_items] > offsets[0] && !data) return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
+    LOCK_CTX(c);
+    CU(cudaSetDevice(c->device));
+    std::vector<uint64_t> rel(n_items + 1, 0);
+    const uint64_t lo = n_items ? offsets[0] : 0;
+    for (size_t f = 0; f <= n_items && n_items; f++) rel[f] = offsets[f] - lo;
+    const uint8_t* d = nullptr;
+    HostSource host;
+    if (n_items && rel[n_items]) {
+        bool is_host = false;
+        if (XetError* e = stage_input(c, data, lo, offsets[n_items], memory, &d, &is_host)) return e;
+        if (is_host) host.base = (const uint8_t*)data + lo;
+    }
+    RunOptions opt;
+    opt.want_chunks = true;
+    opt.items = &items;
+    std::vector<uint64_t> exits;
+    opt.item_exit_cuts = &exits;
+    if (XetError* e = run_batch(c, d, host, rel.data(), n_items, opt, out_result)) return e;
+    if (out_exit_cuts)
+        for (size_t i = 0; i < n_items; i++) out_exit_cuts[i] = exits[i];
+    return nullptr;
 }
 
 // -------------------------------------------------------------------------------------- files

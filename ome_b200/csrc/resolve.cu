@@ -99,13 +99,19 @@ struct FileView {
 };
 
 __device__ __forceinline__ FileView file_view(uint32_t f, const uint64_t* file_off, const uint64_t* seg_off,
-                                              RangeWalk range, bool range_mode) {
+                                              RangeWalk range, bool range_mode, const uint64_t* file_walk) {
     FileView v;
     v.f = f;
     v.begin = file_off[f];
     v.end = file_off[f + 1];
-    v.walk_start = range_mode ? range.walk_start : v.begin;
-    v.is_eof = range_mode ? (range.is_eof != 0) : true;
+    if (file_walk) {  // a batch that mixes whole files and byte-range items
+        const uint64_t w = file_walk[f];
+        v.walk_start = w & ~(1ull << 63);
+        v.is_eof = (w >> 63) == 0;
+    } else {
+        v.walk_start = range_mode ? range.walk_start : v.begin;
+        v.is_eof = range_mode ? (range.is_eof != 0) : true;
+    }
     v.seg0 = seg_off[f];
     v.seg1 = seg_off[f + 1];
     return v;
@@ -161,6 +167,7 @@ struct ResolveArgs {
     uint64_t n_segs;
     RangeWalk range;
     bool range_mode;
+    const uint64_t* file_walk;
     SegArrays sa;
 };
 
@@ -175,7 +182,7 @@ __global__ void resolve_spec_kernel(ResolveArgs a) {
     const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= a.n_segs) return;
     const CandIndex ci = cand_index(a);
-    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode, a.file_walk);
     const uint64_t j = s - v.seg0;
     const uint64_t seg_b = v.begin + j * kSegBytes;
     const uint64_t seg_e = min(v.end, seg_b + kSegBytes);
@@ -204,7 +211,7 @@ __global__ void resolve_spec_kernel(ResolveArgs a) {
 __global__ void resolve_sync_kernel(ResolveArgs a) {
     const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= a.n_segs) return;
-    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    const FileView v = file_view(file_of_seg(a.sa.seg_off, a.n_files, s), a.file_off, a.sa.seg_off, a.range, a.range_mode, a.file_walk);
     if (s == v.seg0) return;
     sync_segment(cand_index(a), a.sa, v, s, a.sa.exit_spec[s - 1]);
 }
@@ -214,7 +221,7 @@ __global__ void resolve_fix_kernel(ResolveArgs a) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (f >= a.n_files) return;
-    const FileView v = file_view(f, a.file_off, a.sa.seg_off, a.range, a.range_mode);
+    const FileView v = file_view(f, a.file_off, a.sa.seg_off, a.range, a.range_mode, a.file_walk);
     const CandIndex ci = cand_index(a);
     uint64_t s = v.seg0 + 1;
     while (s < v.seg1) {
@@ -258,7 +265,7 @@ __global__ void resolve_file_counts_kernel(ResolveArgs a, uint32_t* __restrict__
     const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= a.n_files) return;
     file_count[f] = (uint32_t)(a.sa.seg_base[a.sa.seg_off[f + 1]] - a.sa.seg_base[a.sa.seg_off[f]]);
-    first_start[f] = a.range_mode ? a.range.walk_start : a.file_off[f];
+    first_start[f] = a.file_walk ? (a.file_walk[f] & ~(1ull << 63)) : a.range_mode ? a.range.walk_start : a.file_off[f];
 }
 
 int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_t st) {
@@ -274,6 +281,7 @@ int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_
     a.n_segs = b.n_segs;
     a.range = range ? *range : RangeWalk{0, 1};
     a.range_mode = range != nullptr;
+    a.file_walk = b.file_walk;
     a.sa = SegArrays{b.seg_off, b.seg_spec, b.seg_pre, b.seg_spec_n, b.seg_pre_n, b.seg_merge_idx,
                      b.seg_exit_spec, b.seg_exit_true, b.seg_final_n, b.seg_base};
     int n = 0;

@@ -44,6 +44,9 @@ struct PipelineBuffers {
     uint64_t total_bytes;       // bytes addressable from data
     const uint64_t* file_off;   // device [n_files+1], offsets into data
     uint32_t n_files;
+    const uint64_t* file_walk;  // optional device [n_files]: per-file walk (byte-range items in a batch): bits 0..62 =
+                                // absolute position in data of the entry cut, bit 63 set = the item's end is NOT the
+                                // end of its file.  nullptr: every item is a whole file.
     // K1
     uint32_t n_tiles;
     uint32_t* tile_count;       // [n_tiles]

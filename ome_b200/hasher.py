@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 from dataclasses import dataclass
-from typing import Callable, Optional, Sequence
+from typing import Callable, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -256,6 +256,24 @@ class XetHasher:
                                              C.byref(resp)))
         del keep
         return self._take(resp, want_chunks)
+
+    def hash_buffers_ranges(self, data, offsets: Sequence[int], specs: Sequence[Tuple[int, int, int, int]],
+                            memory: int = MEM_AUTO):
+        """Whole files and byte-range items in one batched call (xetgpu_hash_buffers_ranges).  specs[i] =
+        (file_len, range_begin, range_end, entry_cut); a whole file is (len, 0, len, 0).  Returns (ChunkList with
+        file-relative chunk ends, exit cuts per item)."""
+        addr, _, keep = _ptr_of(data)
+        self._order_after_torch(data)
+        off = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = max(off.size - 1, 0)
+        assert len(specs) == n
+        arr = (L.XetGpuRangeSpec * max(n, 1))(*[L.XetGpuRangeSpec(*[int(x) for x in sp]) for sp in specs])
+        exits = (C.c_uint64 * max(n, 1))()
+        resp = C.POINTER(L.XetGpuResult)()
+        _check(self._lib.xetgpu_hash_buffers_ranges(self._ctx, addr, off.ctypes.data_as(C.POINTER(C.c_uint64)), n, memory,
+                                                    WANT_CHUNKS, arr, exits, C.byref(resp)))
+        del keep
+        return self._take(resp, True), [int(exits[i]) for i in range(n)]
 
     def hash_bytes(self, data, memory: int = MEM_AUTO, want_chunks: bool = False, want_xorbs: bool = False) -> ChunkList:
         _, n, _ = _ptr_of(data)

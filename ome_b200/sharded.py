@@ -223,9 +223,12 @@ def splice_at_common_cut(fix_ends, fix_hashes, spec_ends, spec_hashes):
 
 
 def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end: int, group=None,
-                        comm_device: Optional[torch.device] = None, phases: Optional[dict] = None) -> RangeOutcome:
+                        comm_device: Optional[torch.device] = None, phases: Optional[dict] = None,
+                        spec=None) -> RangeOutcome:
     """`piece` holds bytes [begin - lead, end) of the file (tensor / array / buffer the engine accepts,
-    sliceable).  Collective over `group`: ranks must call it with consecutive ranges in rank order."""
+    sliceable).  Collective over `group`: ranks must call it with consecutive ranges in rank order.
+    `spec` = (chunk_ends, chunk_hashes, exit_cut) of the speculative pass when the caller has already run it
+    (as one item of a batched call, `hash_concatenated`)."""
     import time as _time
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     dev = comm_device or torch.device("cpu")
@@ -240,7 +243,9 @@ def hash_file_by_ranges(engine, piece, lead: int, file_len: int, begin: int, end
 
     # 2. speculative pass over the whole range (rank 0's entry is the true one: the file start)
     assumed = 0 if rank == 0 else begin
-    if end > begin or rank == 0:
+    if spec is not None:
+        ends, hashes, exit_cut = spec
+    elif end > begin or rank == 0:
         spec = engine.hash_range(piece, file_len, begin, end, assumed)
         ends, hashes, exit_cut = spec.chunk_ends, spec.chunk_hashes, spec.exit_cut
     else:                                          # empty range: owns no chunk, only passes the carry on
@@ -343,10 +348,11 @@ def hash_concatenated(engine, buf: torch.Tensor, lay: ConcatLayout, plan: Sequen
                       memory: int = 0):
     """One pass over a `plan_concatenated` job.  Collective: every rank calls it with its own buffer/layout.
 
-    Files that lie inside one rank's range are hashed whole, all of them in one batched engine call; a file that
-    straddles a range boundary goes through the byte-range protocol (`exchange_lead` + `hash_file_by_ranges`)
-    inside its own process group `groups[file]` — even-numbered shared files first, then odd-numbered ones, so
-    that no rank waits on a chain of neighbours.  Returns (file_hashes uint8 [n_files, 32] on every rank,
+    Everything a rank holds goes through ONE batched engine call: the files that lie inside its range as whole
+    files, and its pieces of the files that straddle a range boundary as byte-range items hashed speculatively
+    (halo exchanged first).  The shared files then finish the byte-range protocol (`hash_file_by_ranges`: carried
+    cut, fix-up window, record gather, merkle combine) inside their own process groups `groups[file]` —
+    even-numbered shared files first, then odd-numbered ones, so that no rank waits on a chain of neighbours.  Returns (file_hashes uint8 [n_files, 32] on every rank,
     max bytes any fix-up window re-hashed on this rank)."""
     import time as _time
     rank = dist.get_rank()
@@ -354,44 +360,82 @@ def hash_concatenated(engine, buf: torch.Tensor, lay: ConcatLayout, plan: Sequen
     owners, shared = shared_files(plan)
     out = torch.zeros(n_files, 32, dtype=torch.int32)
     t0 = _time.perf_counter()
-    # 1. whole files of this rank: one batched call.  The alignment padding between files is described to the
-    #    engine as spacer "files" (their hashes are dropped).
-    whole = [(k, p) for k, p in enumerate(lay.pieces) if p.whole and p.file_len]
-    for p in lay.pieces:
-        if p.file_len == 0:   # an empty file has no bytes to lay out: ask the engine for its (all-zero) hash directly
-            fr = engine.hash_buffers(buf[:0], np.zeros(2, dtype=np.uint64), memory=memory).files[0]
-            out[p.file] = torch.frombuffer(bytearray(fr.file_hash), dtype=torch.uint8).to(torch.int32)
-    if whole:
-        marks = sorted({x for k, p in whole for x in (lay.offsets[k], lay.offsets[k] + p.file_len)})
-        offsets = np.asarray(marks, dtype=np.uint64)
-        cl = engine.hash_buffers(buf, offsets, memory=memory)
-        slot = {int(o): i for i, o in enumerate(marks[:-1])}
-        for k, p in whole:
-            fr = cl.files[slot[lay.offsets[k]]]
-            out[p.file] = torch.frombuffer(bytearray(fr.file_hash), dtype=torch.uint8).to(torch.int32)
-    if phases is not None:
-        phases["whole_files_ms"] = phases.get("whole_files_ms", 0.0) + (_time.perf_counter() - t0) * 1e3
-    # 2. shared files
-    rehashed = 0
+    # 1. halo exchange for every shared file this rank holds a piece of (even-numbered shared files first, then
+    #    odd-numbered ones: no rank waits on a chain of neighbours)
+    my_shared = {}   # file -> (piece index, lead)
     for parity in (0, 1):
         for j, f in enumerate(shared):
             if j % 2 != parity or rank not in owners[f]:
                 continue
             k = next(i for i, p in enumerate(lay.pieces) if p.file == f)
             p, o, head = lay.pieces[k], lay.offsets[k], lay.headroom[k]
-            g = groups[f]
             ranges = [(q.begin, q.end) for r in owners[f] for q in plan[r] if q.file == f]
-            view = buf[o: o + head + (p.end - p.begin)]
             t1 = _time.perf_counter()
-            lead = exchange_lead(view, head, ranges, group=g)
+            lead = exchange_lead(buf[o: o + head + (p.end - p.begin)], head, ranges, group=groups[f])
             if phases is not None:
                 phases["halo_exchange_ms"] = phases.get("halo_exchange_ms", 0.0) + (_time.perf_counter() - t1) * 1e3
-            res = hash_file_by_ranges(engine, view[head - lead:], lead, p.file_len, p.begin, p.end, group=g,
-                                      comm_device=dev, phases=phases)
+            my_shared[f] = (k, lead)
+    # 2. ONE batched call for everything this rank holds: its whole files and, as byte-range items hashed from the
+    #    assumption "a cut at my range begin", its pieces of the shared files.  The alignment padding / unused
+    #    headroom between items is described to the engine as spacer files (their results are dropped).
+    t0 = _time.perf_counter()
+    for p in lay.pieces:
+        if p.file_len == 0:   # an empty file has no bytes to lay out: ask the engine for its (all-zero) hash directly
+            fr = engine.hash_buffers(buf[:0], np.zeros(2, dtype=np.uint64), memory=memory).files[0]
+            out[p.file] = torch.frombuffer(bytearray(fr.file_hash), dtype=torch.uint8).to(torch.int32)
+    items = []   # (start, end, spec, piece index or -1)
+    for k, p in enumerate(lay.pieces):
+        if p.file_len == 0 or p.end == p.begin:
+            continue
+        if p.whole:
+            items.append((lay.offsets[k], lay.offsets[k] + p.file_len, (p.file_len, 0, p.file_len, 0), k))
+        else:
+            lead = my_shared[p.file][1]
+            d0 = lay.offsets[k] + lay.headroom[k] - lead
+            entry = 0 if p.begin == 0 else p.begin
+            items.append((d0, d0 + lead + (p.end - p.begin), (p.file_len, p.begin, p.end, entry), k))
+    spec_of = {}
+    if items:
+        items.sort()
+        marks, specs, owner = [], [], []
+        pos = items[0][0]
+        for st, en, sp, k in items:
+            if st > pos:   # spacer
+                marks.append(pos); specs.append((st - pos, 0, st - pos, 0)); owner.append(-1)
+            marks.append(st); specs.append(sp); owner.append(k)
+            pos = en
+        marks.append(pos)
+        if all(k < 0 or lay.pieces[k].whole for k in owner):   # no byte-range item: the plain batched call
+            cl = engine.hash_buffers(buf, np.asarray(marks, dtype=np.uint64), memory=memory)
+            exits = None
+        else:
+            cl, exits = engine.hash_buffers_ranges(buf, np.asarray(marks, dtype=np.uint64), specs, memory=memory)
+        for i, k in enumerate(owner):
+            if k < 0:
+                continue
+            p = lay.pieces[k]
+            if p.whole:
+                out[p.file] = torch.frombuffer(bytearray(cl.files[i].file_hash), dtype=torch.uint8).to(torch.int32)
+            else:
+                e, h = cl.chunks_of(i)
+                spec_of[p.file] = (e, h, exits[i])
+    if phases is not None:
+        phases["batched_pass_ms"] = phases.get("batched_pass_ms", 0.0) + (_time.perf_counter() - t0) * 1e3
+    # 3. carry chain, fix-up window, record gather and merkle combine per shared file
+    rehashed = 0
+    for parity in (0, 1):
+        for j, f in enumerate(shared):
+            if j % 2 != parity or rank not in owners[f]:
+                continue
+            k, lead = my_shared[f]
+            p, o, head = lay.pieces[k], lay.offsets[k], lay.headroom[k]
+            view = buf[o: o + head + (p.end - p.begin)]
+            res = hash_file_by_ranges(engine, view[head - lead:], lead, p.file_len, p.begin, p.end, group=groups[f],
+                                      comm_device=dev, phases=phases, spec=spec_of.get(f))
             rehashed = max(rehashed, res.rehashed_bytes)
             if res.file_hash is not None:
                 out[f] = torch.frombuffer(bytearray(res.file_hash), dtype=torch.uint8).to(torch.int32)
-    # 3. every rank ends with every file hash (rows are non-zero on exactly one rank: a sum is a gather)
+    # 4. every rank ends with every file hash (rows are non-zero on exactly one rank: a sum is a gather)
     t2 = _time.perf_counter()
     if dist.get_world_size() > 1:
         t = out.to(dev)

@@ -49,6 +49,26 @@ class OracleEngine:
             files.append(_File(r.file_hash, int(r.chunk_ends.size)))
         return _List(files)
 
+    def hash_buffers_ranges(self, data, offsets, specs, memory=0):
+        """Whole files and byte-range items in one call; returns (list-like with .files / .chunks_of, exit cuts)."""
+        a = _np(data)
+        files, chunks, exits = [], [], []
+        for i, (flen, begin, end, entry) in enumerate(specs):
+            d = a[int(offsets[i]):int(offsets[i + 1])]
+            if begin == 0 and end == flen:
+                r = xet_oracle.hash_file(d)
+                files.append(_File(r.file_hash, int(r.chunk_ends.size)))
+                chunks.append((r.chunk_ends, r.chunk_hashes))
+                exits.append(int(r.chunk_ends[-1]) if r.chunk_ends.size else 0)
+            else:
+                r = self.hash_range(d, flen, begin, end, entry)
+                files.append(_File(bytes(32), int(r.chunk_ends.size)))
+                chunks.append((r.chunk_ends, r.chunk_hashes))
+                exits.append(int(r.exit_cut))
+        out = _List(files)
+        out.chunks_of = lambda i: chunks[i]
+        return out, exits
+
     def merkle_from_chunks(self, hashes, sizes):
         if hasattr(hashes, "numpy"):
             hashes, sizes = hashes.cpu().numpy().reshape(-1, 32), sizes.cpu().numpy().astype(np.uint64)

@@ -512,3 +512,60 @@ def test_xorb_formation_matches_oracle(hasher, tmp_path):
         small.close()
     _check_xorbs(cl2, datas)
     assert hasher.hash_files(paths).xorbs is None
+
+
+def test_whole_files_and_byte_range_items_in_one_batch(hasher):
+    """xetgpu_hash_buffers_ranges: what a rank of a byte-range partitioned job holds, in ONE batched call."""
+    import ome_b200
+    LEAD = ome_b200.hasher.RANGE_LEAD
+    A = xet_inputs.splitmix_bytes(71, (3 << 20) + 17)
+    B = xet_inputs.splitmix_bytes(72, (9 << 20) + 5)
+    Cc = xet_inputs.build([["splitmix", 73, 1 << 20], ["zeros", 4 << 20]])
+    refB, refC = xet_oracle.hash_file(B), xet_oracle.hash_file(Cc)
+
+    def true_entry(ref, begin):   # last cut <= begin
+        e = [int(x) for x in ref.chunk_ends if x <= begin]
+        return e[-1] if e else 0
+
+    b1, b2 = 3 << 20, 6 << 20
+    items = [  # (data, spec, ref, file bytes)
+        (A, (A.size, 0, A.size, 0), None),
+        (B[b1 - LEAD:b2], (B.size, b1, b2, true_entry(refB, b1)), refB),            # middle range, true entry
+        (np.zeros(0, np.uint8), (0, 0, 0, 0), None),                               # empty whole file
+        (Cc[:2 << 20], (Cc.size, 0, 2 << 20, 0), refC),                            # first range: not the end of the file
+        (B[b2 - LEAD:], (B.size, b2, B.size, true_entry(refB, b2)), refB),          # last range: flushes the tail
+        (B[b1 - LEAD:b2], (B.size, b1, b2, b1), None),                              # speculative entry (a cut assumed at begin)
+    ]
+    off = np.concatenate([[0], np.cumsum([(d.size + 15) // 16 * 16 for d, _, _ in items])]).astype(np.uint64)
+    buf = np.zeros(int(off[-1]), np.uint8)
+    offs = []
+    for (d, _, _), o in zip(items, off[:-1]):
+        buf[int(o):int(o) + d.size] = d
+        offs += [int(o), int(o) + d.size]
+    # items are not contiguous (16-byte padding): describe the gaps as zero-length whole files? no — give exact extents
+    # through one offsets array by placing the items back to back instead
+    packed = np.concatenate([d for d, _, _ in items])
+    poff = np.concatenate([[0], np.cumsum([d.size for d, _, _ in items])]).astype(np.uint64)
+    cl, exits = hasher.hash_buffers_ranges(packed, poff, [s for _, s, _ in items])
+    check_against_oracle(cl, 0, A)
+    assert cl.files[2].n_chunks == 0 and cl.files[2].file_hash == bytes(32)
+    for k, (d, (flen, begin, end, entry), ref) in enumerate(items):
+        if ref is None:
+            continue
+        want = [(int(e), h) for e, h in zip(ref.chunk_ends, ref.chunk_hashes) if begin < e <= end]
+        ends, hashes = cl.chunks_of(k)
+        assert [int(e) for e in ends] == [e for e, _ in want], k
+        assert np.array_equal(hashes, np.array([h for _, h in want]).reshape(-1, 32)), k
+        assert exits[k] == (want[-1][0] if want else entry), k
+    # the speculative item: same protocol result as the single-item entry point
+    single = hasher.hash_range(B[b1 - LEAD:b2], B.size, b1, b2, b1)
+    ends, hashes = cl.chunks_of(5)
+    assert np.array_equal(ends, single.chunk_ends) and np.array_equal(hashes, single.chunk_hashes) and exits[5] == single.exit_cut
+    # device-resident input gives the same answer
+    import torch
+    dev = torch.from_numpy(packed).cuda()
+    cl2, exits2 = hasher.hash_buffers_ranges(dev, poff, [s for _, s, _ in items], memory=ome_b200.hasher.MEM_DEVICE)
+    assert exits2 == exits and np.array_equal(cl2.chunk_hashes, cl.chunk_hashes) and np.array_equal(cl2.chunk_ends, cl.chunk_ends)
+    with pytest.raises(ome_b200.XetGpuError) as ei:
+        hasher.hash_buffers_ranges(packed, poff, [(1, 0, 1, 0)] * len(items))
+    assert ei.value.code == 1
