@@ -264,9 +264,10 @@ XetError* xetgpu_hash_range(XetGpuContext* ctx, const void* data, int32_t memory
  * files that lie inside its range plus its pieces of the files it shares with its neighbours (BASELINE config 4).
  * Item i is data[offsets[i] .. offsets[i+1]) and is described by specs[i]; a whole file is {len, 0, len, 0}, a
  * byte-range item has the meaning of xetgpu_hash_range's arguments (its data starts `lead` bytes before
- * range_begin).  XETGPU_WANT_CHUNKS is required.  Per item the result holds the chunk list (ends relative to the
- * FILE) and, for whole files, root and file hash (for byte-range items those two fields cover only the item's own
- * chunks and are not a file's); out_exit_cuts[i] (optional) receives the cut to hand to the next range's owner.
+ * range_begin).  Per item the result holds, for whole files, root and file hash (for byte-range items those two
+ * fields cover only the item's own chunks and are not a file's) and, for byte-range items, the chunk list (ends
+ * relative to the FILE; files[i].first_chunk / n_chunks index it) — with XETGPU_WANT_CHUNKS the whole files' chunk
+ * lists are returned as well.  out_exit_cuts[i] (optional) receives the cut to hand to the next range's owner.
  */
 typedef struct {
     uint64_t file_len;

@@ -739,6 +739,7 @@ struct RunOptions {
         uint64_t walk_rel;   // entry cut, relative to the item's first data byte
         bool is_eof;
         uint64_t bias;       // file position of the item's first data byte (added to the chunk ends returned)
+        bool partial;        // a byte-range item (its chunk list is always returned) rather than a whole file
     };
     const std::vector<Item>* items = nullptr;
     std::vector<uint64_t>* item_exit_cuts = nullptr;   // per item: last cut (file position), or the entry cut if none
@@ -921,7 +922,7 @@ static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const
         }
         fr.size = offsets[f + 1] - offsets[f];
         fr.n_chunks = g->h_count[f];
-        fr.first_chunk = (opt.want_chunks ? chunk0 : 0) + g->h_base[f];
+        fr.first_chunk = (opt.want_chunks ? chunk0 : 0) + g->h_base[f];   // (rewritten below for selective readback)
         rb->files.push_back(fr);
     }
     if (g->h_xcount) {
@@ -969,12 +970,54 @@ static XetError* finish_group(XetGpuContext* c, Lane* lane, GroupState* g, const
                 for (uint64_t i = c0; i < c1; i++) rb->ends[i] += bias;
             }
     }
+    if (opt.items && !opt.want_chunks && !opt.resolve_only) {
+        // selective readback: chunk lists of the byte-range items only (a rank's whole shards would be ~50 MB of
+        // records nobody reads); one pinned bounce of the few items' slices
+        uint64_t need = 0;
+        for (size_t f = 0; f < F; f++)
+            if ((*opt.items)[f].partial) need += g->h_count[f];
+        if (need * 40 > lane->h_chunks_cap) {
+            if (lane->h_chunks) cudaFreeHost(lane->h_chunks);
+            lane->h_chunks = nullptr;
+            lane->h_chunks_cap = 0;
+            const uint64_t cap = need * 45 + 4096;
+            CU(cudaMallocHost((void**)&lane->h_chunks, cap));
+            lane->h_chunks_cap = cap;
+        }
+        uint64_t w = 0;
+        for (size_t f = 0; f < F; f++) {
+            if (!(*opt.items)[f].partial || !g->h_count[f]) continue;
+            CU(cudaMemcpyAsync(lane->h_chunks + w * 8, b.out_end + g->h_base[f], g->h_count[f] * 8ull, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(lane->h_chunks + need * 8 + w * 32, b.out_hash + g->h_base[f] * 32, g->h_count[f] * 32ull,
+                               cudaMemcpyDeviceToHost, st));
+            w += g->h_count[f];
+        }
+        if (need) CU(cudaStreamSynchronize(st));
+        rb->ends.resize(chunk0 + need);
+        rb->hashes.resize((chunk0 + need) * 32);
+        if (need) {
+            memcpy(rb->ends.data() + chunk0, lane->h_chunks, need * 8);
+            memcpy(rb->hashes.data() + chunk0 * 32, lane->h_chunks + need * 8, need * 32);
+        }
+        w = 0;
+        const size_t file0 = rb->files.size() - F;
+        for (size_t f = 0; f < F; f++) {
+            XetGpuFileResult& fr = rb->files[file0 + f];
+            fr.first_chunk = chunk0 + w;
+            if (!(*opt.items)[f].partial) continue;
+            const uint64_t bias = (*opt.items)[f].bias;
+            for (uint64_t i = 0; i < g->h_count[f]; i++) rb->ends[chunk0 + w + i] += bias;
+            w += g->h_count[f];
+        }
+    }
     if (opt.items && opt.item_exit_cuts) {
         opt.item_exit_cuts->assign(F, 0);
+        const size_t file0 = rb->files.size() - F;
         for (size_t f = 0; f < F; f++) {
             const RunOptions::Item& it = (*opt.items)[f];
-            const uint64_t c1 = chunk0 + g->h_base[f] + g->h_count[f];
-            (*opt.item_exit_cuts)[f] = g->h_count[f] && opt.want_chunks ? rb->ends[c1 - 1] : it.bias + it.walk_rel;
+            const bool have = g->h_count[f] && (opt.want_chunks || it.partial);
+            const uint64_t last = rb->files[file0 + f].first_chunk + g->h_count[f];
+            (*opt.item_exit_cuts)[f] = have ? rb->ends[last - 1] : it.partial ? it.bias + it.walk_rel : it.bias + (offsets[f + 1] - offsets[f]);
         }
     }
     if (timing) {
@@ -1079,7 +1122,7 @@ static XetError* run_pipeline(XetGpuContext* c, const uint8_t* d_data, const uin
     if (XetError* e = run_group_sync(c, &c->lanes[0], d_data, offsets, n_files, opt, &rb)) return e;
     float wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     publish_timings(c, rb, n_files ? offsets[n_files] : 0, wall);
-    return build_result(rb, opt.want_chunks, out_result);
+    return build_result(rb, opt.want_chunks || opt.items != nullptr, out_result);
 }
 
 // ---- file groups on two lanes -------------------------------------------------------------------
@@ -1187,7 +1230,7 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
     }
     float wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     publish_timings(c, rb, total, wall);
-    return build_result(rb, opt.want_chunks, out_result);
+    return build_result(rb, opt.want_chunks || opt.items != nullptr, out_result);
 }
 
 static XetError* resolve_memory_kind(const void* data, int32_t memory, bool* is_device) {
@@ -1281,9 +1324,6 @@ extern "C" XetError* xetgpu_hash_buffers_ranges(XetGpuContext* c, const void* da
     if (!c || !out_result || (n_items && (!offsets || !specs)))
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_hash_buffers_ranges");
     *out_result = nullptr;
-    if (!(flags & XETGPU_WANT_CHUNKS))
-        return make_error(XETGPU_ERR_INVALID_CONFIG, "xetgpu_hash_buffers_ranges needs XETGPU_WANT_CHUNKS: a byte-range item's "
-                                                     "result IS its chunk list");
     std::vector<RunOptions::Item> items(n_items);
     for (size_t i = 0; i < n_items; i++) {
         const XetGpuRangeSpec& sp = specs[i];
@@ -1296,7 +1336,8 @@ extern "C" XetError* xetgpu_hash_buffers_ranges(XetGpuContext* c, const void* da
             return make_error(XETGPU_ERR_INVALID_CONFIG, "entry_cut must lie within one maximum chunk before range_begin");
         if (offsets[i + 1] - offsets[i] != sp.range_end - data_pos)
             return make_error(XETGPU_ERR_INVALID_CONFIG, "an item's data must be bytes [range_begin - lead, range_end) of its file");
-        items[i] = RunOptions::Item{sp.entry_cut - data_pos, sp.range_end == sp.file_len, data_pos};
+        items[i] = RunOptions::Item{sp.entry_cut - data_pos, sp.range_end == sp.file_len, data_pos,
+                                    !(sp.range_begin == 0 && sp.range_end == sp.file_len)};
     }
     if (n_items && offsets[n_items] > offsets[0] && !data) return make_error(XETGPU_ERR_INVALID_CONFIG, "data is NULL");
     LOCK_CTX(c);
@@ -1312,7 +1353,7 @@ extern "C" XetError* xetgpu_hash_buffers_ranges(XetGpuContext* c, const void* da
         if (is_host) host.base = (const uint8_t*)data + lo;
     }
     RunOptions opt;
-    opt.want_chunks = true;
+    opt.want_chunks = (flags & XETGPU_WANT_CHUNKS) != 0;   // without it only the byte-range items carry chunk lists
     opt.items = &items;
     std::vector<uint64_t> exits;
     opt.item_exit_cuts = &exits;

@@ -258,10 +258,11 @@ class XetHasher:
         return self._take(resp, want_chunks)
 
     def hash_buffers_ranges(self, data, offsets: Sequence[int], specs: Sequence[Tuple[int, int, int, int]],
-                            memory: int = MEM_AUTO):
+                            memory: int = MEM_AUTO, want_chunks: bool = False):
         """Whole files and byte-range items in one batched call (xetgpu_hash_buffers_ranges).  specs[i] =
-        (file_len, range_begin, range_end, entry_cut); a whole file is (len, 0, len, 0).  Returns (ChunkList with
-        file-relative chunk ends, exit cuts per item)."""
+        (file_len, range_begin, range_end, entry_cut); a whole file is (len, 0, len, 0).  Returns (ChunkList, exit
+        cuts per item); the ChunkList carries the chunk lists (file-relative ends) of the byte-range items, and of the
+        whole files too with want_chunks."""
         addr, _, keep = _ptr_of(data)
         self._order_after_torch(data)
         off = np.ascontiguousarray(offsets, dtype=np.uint64)
@@ -271,7 +272,7 @@ class XetHasher:
         exits = (C.c_uint64 * max(n, 1))()
         resp = C.POINTER(L.XetGpuResult)()
         _check(self._lib.xetgpu_hash_buffers_ranges(self._ctx, addr, off.ctypes.data_as(C.POINTER(C.c_uint64)), n, memory,
-                                                    WANT_CHUNKS, arr, exits, C.byref(resp)))
+                                                    WANT_CHUNKS if want_chunks else 0, arr, exits, C.byref(resp)))
         del keep
         return self._take(resp, True), [int(exits[i]) for i in range(n)]
 

@@ -536,18 +536,17 @@ def test_whole_files_and_byte_range_items_in_one_batch(hasher):
         (B[b2 - LEAD:], (B.size, b2, B.size, true_entry(refB, b2)), refB),          # last range: flushes the tail
         (B[b1 - LEAD:b2], (B.size, b1, b2, b1), None),                              # speculative entry (a cut assumed at begin)
     ]
-    off = np.concatenate([[0], np.cumsum([(d.size + 15) // 16 * 16 for d, _, _ in items])]).astype(np.uint64)
-    buf = np.zeros(int(off[-1]), np.uint8)
-    offs = []
-    for (d, _, _), o in zip(items, off[:-1]):
-        buf[int(o):int(o) + d.size] = d
-        offs += [int(o), int(o) + d.size]
-    # items are not contiguous (16-byte padding): describe the gaps as zero-length whole files? no — give exact extents
-    # through one offsets array by placing the items back to back instead
+    # items packed back to back (byte-range items start at arbitrary alignment inside the batch)
     packed = np.concatenate([d for d, _, _ in items])
     poff = np.concatenate([[0], np.cumsum([d.size for d, _, _ in items])]).astype(np.uint64)
-    cl, exits = hasher.hash_buffers_ranges(packed, poff, [s for _, s, _ in items])
+    cl, exits = hasher.hash_buffers_ranges(packed, poff, [s for _, s, _ in items], want_chunks=True)
     check_against_oracle(cl, 0, A)
+    # without want_chunks only the byte-range items carry chunk lists; hashes and exit cuts are the same
+    lean, exits_lean = hasher.hash_buffers_ranges(packed, poff, [s for _, s, _ in items])
+    assert exits_lean == exits and lean.files[0].file_hash == cl.files[0].file_hash
+    assert lean.chunk_ends.size == sum(cl.files[k].n_chunks for k in (1, 3, 4, 5))
+    for k in (1, 3, 4, 5):
+        assert np.array_equal(lean.chunks_of(k)[0], cl.chunks_of(k)[0]) and np.array_equal(lean.chunks_of(k)[1], cl.chunks_of(k)[1])
     assert cl.files[2].n_chunks == 0 and cl.files[2].file_hash == bytes(32)
     for k, (d, (flen, begin, end, entry), ref) in enumerate(items):
         if ref is None:
@@ -564,7 +563,8 @@ def test_whole_files_and_byte_range_items_in_one_batch(hasher):
     # device-resident input gives the same answer
     import torch
     dev = torch.from_numpy(packed).cuda()
-    cl2, exits2 = hasher.hash_buffers_ranges(dev, poff, [s for _, s, _ in items], memory=ome_b200.hasher.MEM_DEVICE)
+    cl2, exits2 = hasher.hash_buffers_ranges(dev, poff, [s for _, s, _ in items], memory=ome_b200.hasher.MEM_DEVICE,
+                                             want_chunks=True)
     assert exits2 == exits and np.array_equal(cl2.chunk_hashes, cl.chunk_hashes) and np.array_equal(cl2.chunk_ends, cl.chunk_ends)
     with pytest.raises(ome_b200.XetGpuError) as ei:
         hasher.hash_buffers_ranges(packed, poff, [(1, 0, 1, 0)] * len(items))
