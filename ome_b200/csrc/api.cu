@@ -119,6 +119,9 @@ struct XetGpuContext {
     cudaStream_t second_stream = nullptr;  // odd lanes launch here, even lanes on `stream`
     cudaEvent_t ev_fork = nullptr;
     cudaEvent_t ev_gear_done[kMaxLanes] = {};
+    cudaEvent_t ev_head_done[kMaxLanes] = {};   // staged schedule: K2 + work lists of a group are in place
+    cudaEvent_t ev_leaf_done[kMaxLanes] = {};   // staged schedule: the group's leaf kernel has finished
+    int force_staged = -1;                      // XETGPU_STAGED=0/1 overrides the staged-schedule policy
     int force_lanes = -1;  // XETGPU_TWO_LANES=0/1 overrides the two-lane policy (experiments)
     uint64_t min_group_bytes = 256ull << 20;  // smallest file group worth its own lane (XETGPU_MIN_GROUP_BYTES)
     uint8_t* d_input = nullptr;  // device copy of host inputs
@@ -237,6 +240,9 @@ extern "C" XetError* xetgpu_context_new(const XetGpuConfig* config, XetGpuContex
     }
     ok(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (auto& ev : c->ev_gear_done) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto& ev : c->ev_head_done) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto& ev : c->ev_leaf_done) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    if (const char* v = getenv("XETGPU_STAGED")) c->force_staged = atoi(v) ? 1 : 0;
     for (auto& ev : c->stage_free) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     if (const char* v = getenv("XETGPU_TWO_LANES")) c->force_lanes = atoi(v) ? 1 : 0;
     if (const char* v = getenv("XETGPU_MIN_GROUP_BYTES")) {  // test knob: exercise the two-lane path on small inputs
@@ -288,6 +294,10 @@ extern "C" void xetgpu_context_free(XetGpuContext* c) {
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (auto& ev : c->ev_gear_done)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->ev_head_done)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->ev_leaf_done)
         if (ev) cudaEventDestroy(ev);
     if (c->d_input) cudaFree(c->d_input);
     for (auto& p : c->h_stage)
@@ -752,6 +762,7 @@ struct GroupState {
     uint64_t total = 0;
     size_t n_files = 0;
     int launches = 0;
+    uint64_t meta_bytes = 0;
     bool had_h2d = false;
     // pinned readback area
     uint64_t* h_scalars = nullptr;
@@ -769,73 +780,91 @@ struct GroupState {
 
 // Enqueue the whole pipeline for one group on `lane` (no host synchronisation).
 // d_data: device bytes; offsets: host, relative to d_data.
-static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_data, const uint64_t* offsets,
-                              size_t n_files, const RunOptions& opt, GroupState* g,
-                              cudaEvent_t gear_after = nullptr, cudaEvent_t gear_done = nullptr) {
+// Enqueue stages of the pipeline for one group (no host synchronisation).  `stages` is a bit mask:
+//   1  A: plan, workspace, metadata upload, K1 (gear candidates)
+//   2  H: K2 (boundary resolution) + the K3 work lists
+//   4  K: the K3 leaf kernel
+//   8  T: chunk tree, gather, K4 (+ xorbs) and the result readback
+// All on `st`; a caller that spreads the stages over streams orders them with events.  Stage A must come first.
+// d_data: device bytes; offsets: host, relative to d_data.
+static XetError* launch_group_stages(XetGpuContext* c, Lane* lane, const uint8_t* d_data, const uint64_t* offsets,
+                                     size_t n_files, const RunOptions& opt, GroupState* g, int stages, cudaStream_t st,
+                                     cudaEvent_t gear_after = nullptr, cudaEvent_t gear_done = nullptr) {
     const bool timing = (c->flags & XETGPU_CTX_STAGE_TIMING) != 0;
-    const uint64_t total = n_files ? offsets[n_files] : 0;
-    g->total = total;
-    g->n_files = n_files;
-    const bool xorbs = opt.want_xorbs && !opt.resolve_only && !opt.skip_merkle;
-    g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint, xorbs);
-    g->plan.has_items = opt.items != nullptr;
-    const Plan& plan = g->plan;
-    PipelineBuffers& b = g->b;
-    b = PipelineBuffers{};
-    if (XetError* e = ensure_workspace(lane, plan, &b)) return e;
-    b.data = d_data;
-    if (timing)
-        for (int i = 0; i < 4; i++) b.ev_kernel[i] = lane->ev_kernel[i];
-    // metadata upload through pinned memory
     const uint64_t F = n_files;
+    const bool xorbs = opt.want_xorbs && !opt.resolve_only && !opt.skip_merkle;
+    PipelineBuffers& b = g->b;
+    if (stages & 1) {
+        const uint64_t total = n_files ? offsets[n_files] : 0;
+        g->total = total;
+        g->n_files = n_files;
+        g->launches = 0;
+        g->plan = make_plan(offsets, n_files, total, c->cand_cap_hint, xorbs);
+        g->plan.has_items = opt.items != nullptr;
+        const Plan& plan = g->plan;
+        b = PipelineBuffers{};
+        if (XetError* e = ensure_workspace(lane, plan, &b)) return e;
+        b.data = d_data;
+        if (timing)
+            for (int i = 0; i < 4; i++) b.ev_kernel[i] = lane->ev_kernel[i];
+        // metadata upload through pinned memory
+        const uint64_t X = plan.n_xorb_slots;
+        g->meta_bytes = (F + 1) * 32 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256 +
+                        (xorbs ? (F + 1) * 8 + (F + 2) * 4 + (X + 1) * (8 + 8 + 4 + 32) + 64 : 0);
+        if (XetError* e = ensure_meta(lane, g->meta_bytes)) return e;
+        uint64_t* h_off = reinterpret_cast<uint64_t*>(lane->h_meta);
+        uint64_t* h_slot = h_off + (F + 1);
+        uint64_t* h_seg = h_slot + (F + 1);
+        uint64_t* h_walk = h_seg + (F + 1);
+        if (opt.items)
+            for (size_t f = 0; f < F; f++)
+                h_walk[f] = (offsets[f] + (*opt.items)[f].walk_rel) | ((*opt.items)[f].is_eof ? 0ull : 1ull << 63);
+        memcpy(h_off, offsets, (F + 1) * 8);
+        memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
+        memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
+        if (timing) cudaEventRecord(lane->ev[0], st);
+        CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
+        if (opt.items && F) CU(cudaMemcpyAsync((void*)b.file_walk, h_walk, F * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(b.scalars, 0, 64, st));
+        b.sm_count = c->sm_count;
+        cudaError_t gear_err = cudaSuccess;
+        // Two gear passes side by side only fight for shared-memory bandwidth: a group's gear pass starts when the
+        // previous group's is done.
+        if (gear_after) CU(cudaStreamWaitEvent(st, gear_after, 0));
+        g->launches += launch_gear(b, st, &gear_err);
+        if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
+        if (gear_done) CU(cudaEventRecord(gear_done, st));
+        if (timing) cudaEventRecord(lane->ev[1], st);
+    }
+    const Plan& plan = g->plan;
     const uint64_t X = plan.n_xorb_slots;
-    const uint64_t meta_bytes = (F + 1) * 32 + 64 + (F + 2) * 8 + (F + 1) * 4 + (F + 1) * 64 + 256 +
-                                (xorbs ? (F + 1) * 8 + (F + 2) * 4 + (X + 1) * (8 + 8 + 4 + 32) + 64 : 0);
-    if (XetError* e = ensure_meta(lane, meta_bytes)) return e;
-    uint64_t* h_off = reinterpret_cast<uint64_t*>(lane->h_meta);
-    uint64_t* h_slot = h_off + (F + 1);
-    uint64_t* h_seg = h_slot + (F + 1);
-    uint64_t* h_walk = h_seg + (F + 1);
-    if (opt.items)
-        for (size_t f = 0; f < F; f++)
-            h_walk[f] = (offsets[f] + (*opt.items)[f].walk_rel) | ((*opt.items)[f].is_eof ? 0ull : 1ull << 63);
-    memcpy(h_off, offsets, (F + 1) * 8);
-    memcpy(h_slot, plan.slot_off.data(), (F + 1) * 8);
-    memcpy(h_seg, plan.seg_off.data(), (F + 1) * 8);
-    cudaStream_t st = lane->stream;
-    int launches = 0;
-    if (timing) cudaEventRecord(lane->ev[0], st);
-    CU(cudaMemcpyAsync((void*)b.file_off, h_off, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync((void*)b.slot_off, h_slot, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync((void*)b.seg_off, h_seg, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (opt.items && F) CU(cudaMemcpyAsync((void*)b.file_walk, h_walk, F * 8, cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(b.scalars, 0, 64, st));
-    b.sm_count = c->sm_count;
-    cudaError_t gear_err = cudaSuccess;
-    // Two gear passes side by side only fight for shared-memory bandwidth: a group's gear pass starts when the
-    // previous group's (on the other lane) is done, so that it runs beside that group's BLAKE3 pass instead.
-    if (gear_after) CU(cudaStreamWaitEvent(st, gear_after, 0));
-    launches += launch_gear(b, st, &gear_err);
-    if (gear_err != cudaSuccess) return cuda_error(gear_err, "tensor map setup for the gear kernel");
-    if (gear_done) CU(cudaEventRecord(gear_done, st));
-    if (timing) cudaEventRecord(lane->ev[1], st);
-    launches += launch_resolve(b, opt.range, st);
-    if (timing) cudaEventRecord(lane->ev[2], st);
+    if (stages & 2) {
+        g->launches += launch_resolve(b, opt.range, st);
+        if (timing) cudaEventRecord(lane->ev[2], st);
+        if (!opt.resolve_only) g->launches += launch_chunk_hash_stages(b, st, 1);
+    }
+    if ((stages & 4) && !opt.resolve_only) g->launches += launch_chunk_hash_stages(b, st, 2);
+    if (!(stages & 8)) {
+        CU(cudaGetLastError());
+        return nullptr;
+    }
     if (!opt.resolve_only) {
-        launches += launch_chunk_hash(b, st);
-        launches += launch_gather(b, st);
+        g->launches += launch_chunk_hash_stages(b, st, 4);
+        g->launches += launch_gather(b, st);
         if (timing) cudaEventRecord(lane->ev[3], st);
-        if (!opt.skip_merkle) launches += launch_merkle(b, st);
+        if (!opt.skip_merkle) g->launches += launch_merkle(b, st);
         if (xorbs && X) {
-            uint64_t* h_xs = reinterpret_cast<uint64_t*>(lane->h_meta + meta_bytes - (F + 1) * 8 - 8);  // upload area (tail of the block)
+            uint64_t* h_xs = reinterpret_cast<uint64_t*>(lane->h_meta + g->meta_bytes - (F + 1) * 8 - 8);  // upload area (tail of the block)
             memcpy(h_xs, plan.xorb_off.data(), (F + 1) * 8);
             CU(cudaMemcpyAsync((void*)b.xorb_slot_off, h_xs, (F + 1) * 8, cudaMemcpyHostToDevice, st));
-            launches += launch_xorbs(b, st);
+            g->launches += launch_xorbs(b, st);
         }
         if (timing) cudaEventRecord(lane->ev[4], st);
     } else {
-        launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
-                                    b.scalars + kScalarChunks, st);
+        g->launches += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial,
+                                       b.scalars + kScalarChunks, st);
         if (timing) {
             cudaEventRecord(lane->ev[3], st);
             cudaEventRecord(lane->ev[4], st);
@@ -873,8 +902,14 @@ static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_dat
         CU(cudaMemcpyAsync(g->h_xroot, b.xorb_root, X * 32, cudaMemcpyDeviceToHost, st));
     }
     if (timing) cudaEventRecord(lane->ev[5], st);
-    g->launches = launches;
     return nullptr;
+}
+
+// The whole pipeline of one group on its lane's stream.
+static XetError* launch_group(XetGpuContext* c, Lane* lane, const uint8_t* d_data, const uint64_t* offsets,
+                              size_t n_files, const RunOptions& opt, GroupState* g,
+                              cudaEvent_t gear_after = nullptr, cudaEvent_t gear_done = nullptr) {
+    return launch_group_stages(c, lane, d_data, offsets, n_files, opt, g, 15, lane->stream, gear_after, gear_done);
 }
 
 // Result accumulator shared by all groups of one call.
@@ -1148,6 +1183,16 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
     bool two_lanes = !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && (host.base != nullptr || n_files >= 16);
     if (c->force_lanes >= 0 && !opt.range) two_lanes = c->force_lanes == 1;
     if (opt.items) two_lanes = false;   // per-item descriptors are indexed by position in the batch: one group
+    // The staged schedule below (bulk kernels strictly one after the other on one stream, every group's short
+    // latency-bound kernels on the second stream behind the next bulk kernel) is OFF unless XETGPU_STAGED=1: measured
+    // on B200 with config 2 it runs 14.6 ms against 13.7 ms for one group — the small kernels are not free to hide,
+    // they stretch the gear and leaf kernels they run beside by about what they cost alone (4.21 -> 4.46 ms and
+    // 8.31 -> 8.96 ms) and the per-group dependencies add gaps (profiles/r2_summary.md).
+    bool staged = false;
+    if (c->force_staged == 1 && !(c->flags & XETGPU_CTX_NO_OVERLAP) && !opt.range && !opt.items && !opt.resolve_only &&
+        !host.base && n_files >= 2)
+        staged = true;
+    if (staged) two_lanes = true;   // same grouping rule
     if (two_lanes) {
         uint64_t acc = 0;
         for (size_t f = 0; f < n_files; f++) {
@@ -1167,7 +1212,57 @@ static XetError* run_batch(XetGpuContext* c, const uint8_t* d_data, const HostSo
         g->had_h2d = true;
         return ingest_host(c, lane->stream, host.base + lo, hi - lo, const_cast<uint8_t*>(d_data) + lo);
     };
-    if (G <= 1) {
+    if (staged && G >= 2 && G <= (size_t)kMaxLanes) {
+        // Order on the bulk stream B: A0 A1 K0 A2 K1 ... K(G-1)  (A = K1 gear pass, K = K3 leaf kernel: the two kernels
+        // that each fill the SMs never overlap one another); on the small stream S: H0 H1 T0 H2 T1 ... T(G-1)
+        // (H = K2 + work lists, T = chunk tree + gather + K4 + readback), tied to B by events.
+        cudaStream_t B = c->stream, S = c->second_stream;
+        CU(cudaEventRecord(c->ev_fork, B));
+        CU(cudaStreamWaitEvent(S, c->ev_fork, 0));
+        std::vector<GroupState> state(G);
+        std::vector<std::vector<uint64_t>> rel(G);
+        std::vector<uint64_t> group_base(G, 0);
+        auto stage = [&](size_t gi, int stages, cudaStream_t st) -> XetError* {
+            const size_t f0 = cut[gi], f1 = cut[gi + 1];
+            return launch_group_stages(c, &c->lanes[gi], d_data + group_base[gi], rel[gi].data(), f1 - f0, opt, &state[gi], stages,
+                                       st, nullptr, stages == 1 ? c->ev_gear_done[gi] : nullptr);
+        };
+        auto leaf_and_tail = [&](size_t gi) -> XetError* {
+            CU(cudaStreamWaitEvent(B, c->ev_head_done[gi], 0));
+            if (XetError* e = stage(gi, 4, B)) return e;
+            CU(cudaEventRecord(c->ev_leaf_done[gi], B));
+            CU(cudaStreamWaitEvent(S, c->ev_leaf_done[gi], 0));
+            return stage(gi, 8, S);
+        };
+        for (size_t gi = 0; gi < G; gi++) {
+            const size_t f0 = cut[gi], f1 = cut[gi + 1];
+            const uint64_t base_lo = offsets[f0] & ~15ull;   // 16-byte aligned group base (TMA), as below
+            group_base[gi] = base_lo;
+            rel[gi].assign(f1 - f0 + 1, 0);
+            for (size_t f = f0; f <= f1; f++) rel[gi][f - f0] = offsets[f] - base_lo;
+            if (XetError* e = stage(gi, 1, B)) return e;
+            // the head of group gi goes on S before the tail of gi - 1: it is what the bulk stream waits for next
+            CU(cudaStreamWaitEvent(S, c->ev_gear_done[gi], 0));
+            if (XetError* e = stage(gi, 2, S)) return e;
+            CU(cudaEventRecord(c->ev_head_done[gi], S));
+            if (gi)
+                if (XetError* e = leaf_and_tail(gi - 1)) return e;
+        }
+        if (XetError* e = leaf_and_tail(G - 1)) return e;
+        // the call returns with everything complete on both streams, and B ordered after S for the caller
+        CU(cudaEventRecord(c->ev_fork, S));
+        CU(cudaStreamWaitEvent(B, c->ev_fork, 0));
+        CU(cudaStreamSynchronize(S));
+        CU(cudaStreamSynchronize(B));
+        for (size_t gi = 0; gi < G; gi++) {
+            bool overflow = false;
+            if (XetError* e = finish_group(c, &c->lanes[gi], &state[gi], rel[gi].data(), opt, &rb, &overflow)) return e;
+            if (overflow)
+                if (XetError* e = run_group_sync(c, &c->lanes[gi], d_data + group_base[gi], rel[gi].data(), cut[gi + 1] - cut[gi],
+                                                 opt, &rb))
+                    return e;
+        }
+    } else if (G <= 1) {
         GroupState dummy;
         if (XetError* e = ingest(&c->lanes[0], 0, total, &dummy)) return e;
         // the copy is on lane 0's stream, in front of the pipeline: timing of it is taken there

@@ -280,23 +280,35 @@ void init_chunk_hash_kernels() {
     cudaFuncSetAttribute(leaf_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLeafSmem);
 }
 
-int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st) {
-    int n = launch_chunk_bookkeeping(b, st);
+// The stage in three parts, so that a caller can place them on different streams: `stages` is a bit mask of
+// 1 = bookkeeping (work lists), 2 = the leaf kernel, 4 = dense chunk numbering + chunk tree.
+int launch_chunk_hash_stages(const PipelineBuffers& b, cudaStream_t st, int stages) {
+    int n = 0;
+    if (stages & 1) n += launch_chunk_bookkeeping(b, st);
     if (b.n_slots == 0 || b.n_groups_cap == 0) return n;
-    const uint64_t warps = (b.n_groups_cap + 31) / 32;
-    const unsigned blocks = (unsigned)((warps + kLeafWarpsPerCta - 1) / kLeafWarpsPerCta);
-    if (b.ev_kernel[2]) cudaEventRecord(b.ev_kernel[2], st);
-    leaf_group_kernel<<<blocks, kLeafThreads, kLeafSmem, st>>>(b.data, b.scalars, b.group_chunk, b.group_off,
-                                                               b.chunk_start, b.chunk_len, b.group_cv, b.chunk_hash);
-    if (b.ev_kernel[3]) cudaEventRecord(b.ev_kernel[3], st);
-    // dense chunk numbering: exclusive scan of the per-file chunk counts (+ the batch's chunk count), also used by
-    // the gather and by the xorb pass
-    n += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial, b.scalars + kScalarChunks, st);
-    const uint64_t want = (b.n_slots * kTreeLanes + kTreeThreads - 1) / kTreeThreads;
-    const unsigned tblocks = (unsigned)std::min<uint64_t>(want, (uint64_t)b.sm_count * 16);
-    chunk_tree_kernel<<<tblocks ? tblocks : 1, kTreeThreads, 0, st>>>(b.scalars, b.n_files, b.file_chunk_base, b.slot_off,
-                                                                      b.slot_groups, b.group_off, b.group_cv, b.chunk_hash);
-    return n + 2;
+    if (stages & 2) {
+        const uint64_t warps = (b.n_groups_cap + 31) / 32;
+        const unsigned blocks = (unsigned)((warps + kLeafWarpsPerCta - 1) / kLeafWarpsPerCta);
+        if (b.ev_kernel[2]) cudaEventRecord(b.ev_kernel[2], st);
+        leaf_group_kernel<<<blocks, kLeafThreads, kLeafSmem, st>>>(b.data, b.scalars, b.group_chunk, b.group_off,
+                                                                   b.chunk_start, b.chunk_len, b.group_cv, b.chunk_hash);
+        if (b.ev_kernel[3]) cudaEventRecord(b.ev_kernel[3], st);
+        n++;
+    }
+    if (stages & 4) {
+        // dense chunk numbering: exclusive scan of the per-file chunk counts (+ the batch's chunk count), also used
+        // by the gather and by the xorb pass
+        n += launch_scan_u32(b.file_count, b.file_chunk_base, b.n_files, b.scan_partial, b.scalars + kScalarChunks, st);
+        const uint64_t want = (b.n_slots * kTreeLanes + kTreeThreads - 1) / kTreeThreads;
+        const unsigned tblocks = (unsigned)std::min<uint64_t>(want, (uint64_t)b.sm_count * 16);
+        chunk_tree_kernel<<<tblocks ? tblocks : 1, kTreeThreads, 0, st>>>(b.scalars, b.n_files, b.file_chunk_base,
+                                                                          b.slot_off, b.slot_groups, b.group_off,
+                                                                          b.group_cv, b.chunk_hash);
+        n++;
+    }
+    return n;
 }
+
+int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st) { return launch_chunk_hash_stages(b, st, 7); }
 
 }  // namespace xetgpu

@@ -131,6 +131,7 @@ struct RangeWalk {
 };
 int launch_resolve(const PipelineBuffers& b, const RangeWalk* range, cudaStream_t st);
 int launch_chunk_hash(const PipelineBuffers& b, cudaStream_t st);
+int launch_chunk_hash_stages(const PipelineBuffers& b, cudaStream_t st, int stages);  // 1 work lists, 2 leaf kernel, 4 tree
 int launch_merkle(const PipelineBuffers& b, cudaStream_t st);
 int launch_gather(const PipelineBuffers& b, cudaStream_t st);
 // Xorb formation over the dense per-file chunk lists (after launch_gather and launch_merkle): greedy packing into
