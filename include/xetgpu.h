@@ -20,8 +20,8 @@
  *     internally; it must not be used during xetgpu_context_free  [pkg/xet/README.md:76,88]
  *   - progress / cancellation use the reference's callback shapes   [pkg/xet/xet.h:22-40]; handlers run on
  *     library threads with no library lock held, but the call that invokes them is still in progress: a handler
- *     may call xetgpu_context_set_progress_callback / xetgpu_last_timings, while a hashing call on the same
- *     context from inside a handler is refused with code 1 (it would wait for itself)
+ *     may call xetgpu_context_set_progress_callback / xetgpu_last_timings, while a hashing call made from
+ *     inside a handler (on any handle of this library) is refused with code 1 (it could wait for itself)
  *   - a no-op versioned symbol lets the cgo preamble fail at link time on a mismatch
  *                                                       [pkg/xet/xet.h:94; pkg/xet/xet.go:11-13]
  * No type in this header depends on CUDA or PyTorch; device pointers travel as void*.

@@ -146,11 +146,19 @@ struct XetGpuContext {
 // Entry-point lock.  Calls on one context serialise on c->mu.  A progress / cancellation callback runs on a thread
 // that is inside such a call; if it calls a hashing entry point of the SAME context it would wait for itself, so
 // that case is detected and refused with XETGPU_ERR_INVALID_CONFIG instead of deadlocking.
+// Set while a user callback (progress or cancellation) runs on this thread: hashing entry points refuse to start
+// from inside one, whichever handle they are given (a multi-device call runs callbacks on its worker threads).
+static thread_local int tl_in_callback = 0;
+struct CallbackScope {
+    CallbackScope() { tl_in_callback++; }
+    ~CallbackScope() { tl_in_callback--; }
+};
+
 struct CtxGuard {
     XetGpuContext* c;
     bool ok;
     explicit CtxGuard(XetGpuContext* ctx) : c(ctx), ok(true) {
-        if (c->owner.load() == std::this_thread::get_id()) {
+        if (tl_in_callback || c->owner.load() == std::this_thread::get_id()) {
             ok = false;
             return;
         }
@@ -336,6 +344,7 @@ static void report_progress(XetGpuContext* c, const XetProgressUpdate& u, bool f
         cb = c->progress;
         user = c->progress_user;
     }
+    CallbackScope scope;
     cb(&u, user);
 }
 
@@ -1470,7 +1479,9 @@ static XetError* stat_regular(const char* path, uint64_t* size) {
 }
 
 static bool cancelled(const XetCancellationToken* cancel) {
-    return cancel && cancel->callback && cancel->callback(cancel->user_data);
+    if (!cancel || !cancel->callback) return false;
+    CallbackScope scope;
+    return cancel->callback(cancel->user_data);
 }
 
 // Progress of one xetgpu_hash_files call (or of one device's share of a multi-device call).
@@ -2140,6 +2151,9 @@ extern "C" XetError* xetgpu_multi_hash_files(XetGpuMulti* m, const char* const* 
     if (!m || !out_result || (n_files && !paths))
         return make_error(XETGPU_ERR_INVALID_CONFIG, "NULL argument to xetgpu_multi_hash_files");
     *out_result = nullptr;
+    if (tl_in_callback)
+        return make_error(XETGPU_ERR_INVALID_CONFIG, "re-entrant call: a progress or cancellation callback called a hashing "
+                                                     "entry point of the library");
     std::lock_guard<std::mutex> lk(m->mu);
     std::vector<uint64_t> sizes(n_files);
     uint64_t all_bytes = 0;

@@ -187,3 +187,24 @@ def test_file_larger_than_the_device_budget_streams_in_pieces(tmp_path):
         h.verify_file(paths[0], cl.files[0].hex)
     finally:
         h.close()
+
+
+def test_multi_reentrant_call_from_handler_is_refused(tmp_path, monkeypatch):
+    import ome_b200
+    monkeypatch.setenv("XETGPU_MULTI_MIN_BYTES", str(1 << 20))
+    paths, datas = _write(tmp_path, [[["splitmix", 51, 24 << 20]], [["splitmix", 52, 9 << 20]]])
+    got = {}
+    with ome_b200.XetMultiHasher([0, 0]) as m:
+        def handler(_u):
+            if "err" not in got:
+                try:
+                    m.hash_files(paths[:1])
+                    got["err"] = None
+                except ome_b200.XetGpuError as e:
+                    got["err"] = e
+
+        m.set_progress_handler(handler, throttle_ms=0)
+        cl = m.hash_files(paths)
+        m.set_progress_handler(None)
+        _check(cl, datas)
+    assert got["err"] is not None and got["err"].code == 1 and "re-entrant" in got["err"].message
