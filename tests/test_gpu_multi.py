@@ -208,3 +208,29 @@ def test_multi_reentrant_call_from_handler_is_refused(tmp_path, monkeypatch):
         m.set_progress_handler(None)
         _check(cl, datas)
     assert got["err"] is not None and got["err"].code == 1 and "re-entrant" in got["err"].message
+
+
+def test_in_process_plan_equals_the_multi_process_plan(tmp_path, monkeypatch):
+    """xetgpu_multi_plan (C++, one process) lays files out exactly as sharded.plan_concatenated (Python, one process
+    per GPU) does: the two forms of the config-4 partition cannot drift apart."""
+    import ome_b200
+    from ome_b200 import sharded
+    monkeypatch.setenv("XETGPU_MULTI_MIN_BYTES", "1")
+    rng = np.random.default_rng(11)
+    for trial, sizes in enumerate([[3 << 20, 0, 5 << 20, 70001, 2 << 20], [20 << 20], [6 << 20] * 4,
+                                   [int(x) for x in rng.integers(0, 3_000_000, 23)], [0, 0], [1 << 20, 131136 + 4096, 7]]):
+        d = tmp_path / f"t{trial}"
+        d.mkdir()
+        paths = []
+        for i, n in enumerate(sizes):
+            p = d / f"f{i}.bin"
+            with open(p, "wb") as f:
+                f.truncate(n)               # sparse: only the sizes matter for the plan
+            paths.append(str(p))
+        for world in (1, 2, 3, 5):
+            with ome_b200.XetMultiHasher([0] * world) as m:
+                got = m.plan(paths, tensor_snap=False)
+            used = min(world, max(1, sum(sizes)))    # the library uses fewer devices than listed for tiny jobs
+            want = [(r, p.file, p.begin, p.end) for r, pieces in enumerate(sharded.plan_concatenated(sizes, used))
+                    for p in pieces]
+            assert got == want, (trial, world)
